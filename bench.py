@@ -1,0 +1,335 @@
+#!/usr/bin/env python3
+"""bench.py -- AWFL dycore time-step throughput (cell-updates/s) on N B200s of one node.
+
+  python bench.py --gpus N --steps K --warmup W              # the CUDA path (this repo)
+  python bench.py --impl reference --gpus N --steps K ...    # the reference's own CPU code (oracle/_ref, OpenMP)
+
+A "step" is one Dycore::timeStep over the whole ensemble batch (= `ncycles` SSPRK3 sub-cycles); one cell-update is one
+(k,j,i,iens) cell advanced by one sub-cycle (3 Runge-Kutta stages), SURVEY.md 8(d). Workload at N=1 is BASELINE.json
+configs[1]: MMF-style batched 2-D CRMs 64x58, nens=4096, WENO ord=5, one tracer (water vapour), supercell sounding with
+per-member wind offsets and a seeded temperature perturbation (pam_b200/synthetic.py). N>1: every rank owns its own
+4096 members (weak scaling, the way MMF places a fixed number of CRMs per rank); no data-path collective exists
+(CRMs are independent) -- NCCL only carries the timing max and the global mass diagnostic.
+
+Prints ONE JSON line (rank 0).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    # name: (nz, ny, nx, nens_per_gpu, ord, tracer set)
+    "C2": dict(nz=58, ny=1, nx=64, nens=4096, ord=5, nt=1, desc="2-D 64x58, nens=4096/GPU, ord=5, NT=1"),
+    "C3": dict(nz=58, ny=32, nx=32, nens=128, ord=5, nt=1, desc="3-D 32x32x58, nens=128/GPU, ord=5, NT=1"),
+    "C4": dict(nz=58, ny=1, nx=128, nens=2048, ord=5, nt=1, desc="2-D 128x58, nens=2048/GPU, ord=5, NT=1"),
+    "C5": dict(nz=58, ny=1, nx=64, nens=4096, ord=5, nt=10, desc="2-D 64x58, nens=4096/GPU, ord=5, NT=10 (P3+SHOC tracers)"),
+    "tiny": dict(nz=16, ny=1, nx=16, nens=64, ord=5, nt=1, desc="2-D 16x16, nens=64 (plumbing check)"),
+}
+CRM_DT = 1.0
+
+
+def build_case(w, ens_offset=0, nens=None):
+    """Synthetic fields are generated for a 32-member tile and tiled along the ensemble axis with the per-member
+    wind offset re-applied, so that set-up of 15M-cell fields stays cheap; values still differ member to member."""
+    from pam_b200 import synthetic as syn
+    nens = nens or w["nens"]
+    tr = syn.TRACERS_NT1 if w["nt"] == 1 else syn.TRACERS_P3_SHOC
+    base_n = min(nens, 68)   # 68 = 4*17: covers every residue of the %17, %7, %5, %3 member variations
+    case = syn.make_case(w["nz"], w["ny"], w["nx"], base_n, tracers=tr, grid="equal", ens_offset=ens_offset)
+    if base_n < nens:
+        reps = (nens + base_n - 1) // base_n
+        for k, v in case["fields"].items():
+            case["fields"][k] = np.ascontiguousarray(np.tile(v, (1, 1, 1, reps))[..., :nens])
+        case["nens"] = nens
+    return case
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md)."""
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+            "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + q, "--format=csv,noheader,nounits",
+                                          "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.th = threading.Thread(target=self._read, daemon=True)
+            self.th.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            pass
+        sm = [float(r[0]) for r in self.rows if len(r) >= 7 and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) >= 7 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(len(r) >= 7 and r[3 + i].lower().startswith("active") for r in self.rows)]
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
+                "samples": len(sm)}
+
+
+def cpu_reference_rate(w, seconds_target=12.0, warm=1, steps=None, nens=None):
+    """Times the reference's own CPU implementation (oracle/_ref, OpenMP build of the unmodified reference) on a bounded
+    sample of the workload: same grid, order, tracers and inputs, fewer ensemble members. Returns the cpu_baseline dict
+    and the per-step times."""
+    from oracle import reflib
+    cores = os.cpu_count() or 1
+    os.environ.setdefault("OMP_NUM_THREADS", str(cores))
+    os.environ.setdefault("OMP_PROC_BIND", "close")
+    kind = "reference"
+    if not reflib.available(w["ord"], omp=True):
+        raise RuntimeError("oracle/_ref/libpam_ref_ord%d_omp.so is missing (build it with __graft_entry__.build() where "
+                           "/root/reference exists)" % w["ord"])
+    nens = nens or max(8, min(w["nens"], 2 * cores))
+    case = build_case(w, nens=nens)
+    r = reflib.RefDycore(w["nz"], w["ny"], w["nx"], nens, case["xlen"], case["ylen"], case["zint"], tracers=case["tracers"],
+                         consts=case["consts"], crm_dt=CRM_DT, ord=w["ord"], omp=True)
+    r.set_fields(case["fields"])
+    r.declare_hydrostatic_raw(); r.declare_hydrostatic_raw()    # twice: SURVEY.md F2/F4
+    dt = r.compute_time_step()
+    ncycles = int(np.ceil(CRM_DT / dt))
+    for _ in range(warm):
+        r.time_steps_raw(1)
+    t1 = r.time_steps_raw(1)
+    if steps is None:
+        steps = int(max(2, min(50, seconds_target / max(t1, 1e-3))))
+    times = [r.time_steps_raw(1) for _ in range(steps)]
+    upd = w["nz"] * w["ny"] * w["nx"] * nens * ncycles
+    rate = upd * len(times) / sum(times)
+    cb = {"value": rate, "unit": "cell-updates/s", "cores": cores, "kind": kind,
+          "sample": "%s with nens=%d (of %d), ncycles=%d, %d timed Dycore::timeStep calls of the unmodified reference "
+                    "(g++ -O3 -march=x86-64-v3, YAKL OpenMP backend, OMP_NUM_THREADS=%d)" % (w["desc"], nens, w["nens"], ncycles, len(times), cores)}
+    return cb, times, ncycles, upd
+
+
+def run_reference_arm(args, w):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cb, times, ncycles, upd = cpu_reference_rate(w, warm=max(1, args.warmup), steps=args.steps)
+    ms = 1e3 * sum(times) / len(times)
+    line = {"impl": "reference", "metric": "AWFL dycore cell-updates/sec", "value": cb["value"], "unit": "cell-updates/s",
+            "n_gpus": args.gpus, "steps": len(times), "warmup": max(1, args.warmup), "ms_per_step": ms, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": args.workload + ": " + w["desc"], "crm_dt": CRM_DT, "ncycles": ncycles,
+                       "cell_updates_per_step": upd},
+            "cpu_baseline": cb,
+            "e2e": {"value": cb["value"], "unit": "cell-updates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="C2", choices=sorted(WORKLOADS))
+    ap.add_argument("--ord", type=int, default=None)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    args = ap.parse_args()
+    w = dict(WORKLOADS[args.workload])
+    if args.ord:
+        w["ord"] = args.ord
+        w["desc"] = w["desc"].replace("ord=5", "ord=%d" % args.ord)
+    if args.impl == "reference":
+        run_reference_arm(args, w)
+        return
+    args.warmup = max(args.warmup, 3)
+
+    import torch
+    import torch.distributed as dist
+    from pam_b200 import PamCoupler, Dycore, roofline
+    from pam_b200.parallel import shard_range, global_mass
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise RuntimeError("bench.py needs a CUDA device: the AWFL path has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    # ---- set-up (untimed): this rank's shard of the global ensemble ----
+    nens_global = w["nens"] * world
+    e0, e1 = shard_range(nens_global, rank, world)
+    case = build_case(w, ens_offset=e0, nens=e1 - e0)
+    c = PamCoupler(dev)
+    c.set_option("crm_dt", CRM_DT)
+    for k in ("R_d", "cp_d", "R_v", "cp_v", "p0", "grav"):
+        c.set_option(k, case["consts"][k])
+    c.allocate_coupler_state(w["nz"], w["ny"], w["nx"], e1 - e0)
+    c.set_grid(case["xlen"], case["ylen"], case["zint"])
+    for name, pos, adds in case["tracers"]:
+        c.add_tracer(name, name, pos, adds)
+    d = Dycore(w["ord"])
+    d.init(c)
+    dm = c.get_data_manager_device_readwrite()
+    names = ["density_dry", "uvel", "vvel", "wvel", "temp"] + c.get_tracer_names()
+    for n in names:
+        dm.get(n).copy_(torch.from_numpy(case["fields"][n]))
+    d.declare_current_profile_as_hydrostatic(c)
+    init = {n: dm.get(n).clone() for n in names}
+    ncell = w["nz"] * w["ny"] * w["nx"] * (e1 - e0)
+    mass0 = d.compute_mass(c)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    # ---- warm-up ----
+    ncycles = 0
+    for _ in range(args.warmup):
+        ncycles = d.timeStep(c)
+    # ---- timed region: K steps, device-resident fields, CUDA events on the launching stream ----
+    l0 = d.launch_count()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+        time.sleep(0.3)
+    barrier()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    d.profile_begin()
+    ev0.record()
+    cyc = []
+    for _ in range(args.steps):
+        cyc.append(d.timeStep(c))
+    ev1.record()
+    prof = d.profile_end()
+    barrier()
+    ms_total = ev0.elapsed_time(ev1)
+    clocks = sampler.stop() if rank == 0 else None
+    launches = d.launch_count() - l0
+    t = torch.tensor([ms_total], dtype=torch.float64, device=dev)
+    upd = torch.tensor([float(ncell) * sum(cyc)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(upd, op=dist.ReduceOp.SUM)
+    ms_total = float(t.item())
+    value = float(upd.item()) / (ms_total * 1e-3)
+
+    # global conservation diagnostic (the only collective on this path; untimed)
+    mass1 = d.compute_mass(c)
+    gm0, gm1 = global_mass(mass0, nens_global), global_mass(mass1, nens_global)
+    nt = len(case["tracers"])
+    mass_drift = float(abs(gm1[nt] - gm0[nt]) / abs(gm0[nt]))
+
+    # ---- end-to-end through the C ABI with HOST buffers (pinned), H2D + step + D2H inside the timed region ----
+    e2e = None
+    if not args.no_e2e:
+        host = [torch.empty(init[n].shape, dtype=torch.float64).pin_memory() for n in names]
+        for hbuf, n in zip(host, names):
+            hbuf.copy_(init[n])
+        harr = [hbuf.numpy() for hbuf in host]
+        for _ in range(2):
+            d.time_step_host(harr, CRM_DT)
+        barrier()
+        t0 = time.perf_counter()
+        ecyc = []
+        nst = max(2, min(args.steps, 5))
+        for _ in range(nst):
+            ecyc.append(d.time_step_host(harr, CRM_DT))
+        torch.cuda.synchronize(dev)
+        te = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+        eu = torch.tensor([float(ncell) * sum(ecyc)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(te, op=dist.ReduceOp.MAX)
+            dist.all_reduce(eu, op=dist.ReduceOp.SUM)
+        fb = 8 * ncell * len(names)
+        e2e = {"value": float(eu.item()) / float(te.item()), "unit": "cell-updates/s", "h2d_bytes_per_step": fb * world,
+               "d2h_bytes_per_step": fb * world, "steps": nst,
+               "note": "awfl_time_step_host: pinned host fields -> device, Dycore::timeStep, device -> host, every step"}
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    # ---- roofline of the dominant kernel (largest share of device time), measured live with CUDA events ----
+    tot_ms = sum(v[0] for v in prof.values())
+    dom = max(prof, key=lambda k: prof[k][0])
+    dom_ms, dom_n = prof[dom]
+    ndir = 2 if w["ny"] == 1 else 3
+    fp64_peak = d.measure_fp64_peak(1 << 14)
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    hbm_peak = peaks.get("hbm_gbs", 6650.0)
+    hbm_src = "measured (MEASURED_PEAKS.json)" if "hbm_gbs" in peaks else "fallback (B200_PROFILING.md)"
+    if dom.startswith("state_"):
+        fl = roofline.state_sweep_flops_per_cell(w["ord"]) * ncell
+        by = roofline.state_sweep_bytes_per_cell(last=dom == "state_z") * ncell
+    elif dom.startswith("tracer_") and dom != "tracer_upd":
+        fl = (roofline.recon_flops(w["ord"])[0] + 4) * ncell * nt
+        by = 8 * 4 * ncell * nt
+    else:
+        fl, by = 40.0 * ncell * nt, 8 * 12 * ncell * nt
+    dur = dom_ms / max(dom_n, 1) * 1e-3
+    roof = {"bound": "fp64", "kernel": dom, "achieved": fl / dur / 1e12, "peak": fp64_peak, "unit": "TFLOP/s",
+            "frac": fl / dur / 1e12 / fp64_peak, "traffic": None,
+            "peak_source": "DFMA-chain microbenchmark run in this process (awfl_measure_fp64_peak); FP64 peak is not in MEASURED_PEAKS.json",
+            "flops_per_launch": fl, "avg_launch_ms": dur * 1e3, "share_of_step": dom_ms / tot_ms,
+            "hbm": {"achieved": by / dur / 1e9, "peak": hbm_peak, "unit": "GB/s", "frac": by / dur / 1e9 / hbm_peak,
+                    "bytes_per_launch": by, "peak_source": hbm_src},
+            "note": "the AWFL step is FP64-pipe bound (SURVEY.md 8d: 32-60 flop/B vs a ridge of ~6), so the binding roofline "
+                    "is the FP64 one; flops are the REFERENCE algorithm's count (pam_b200/roofline.py)"}
+    # whole-step view
+    step_fl = roofline.flops_per_cell_update(w["ord"], w["nt"], ndir) * float(ncell) * sum(cyc)
+    step_by = roofline.bytes_per_cell_update(w["nt"]) * float(ncell) * sum(cyc)
+    whole = {"tflops": step_fl / (ms_total * 1e-3) / 1e12, "frac_fp64": step_fl / (ms_total * 1e-3) / 1e12 / fp64_peak,
+             "gbs_algorithmic": step_by / (ms_total * 1e-3) / 1e9, "frac_hbm": step_by / (ms_total * 1e-3) / 1e9 / hbm_peak}
+    kernels = {k: {"ms_per_step": v[0] / args.steps, "launches_per_step": v[1] / args.steps, "share": v[0] / tot_ms}
+               for k, v in prof.items() if v[1]}
+
+    cpu_baseline = None
+    if not args.no_cpu_baseline and world == 1:
+        try:
+            cpu_baseline, _, _, _ = cpu_reference_rate(w)
+        except Exception as ex:   # the oracle always exists in a built tree; say why if not
+            cpu_baseline = {"value": None, "unit": "cell-updates/s", "cores": os.cpu_count(), "kind": "reference", "sample": "failed: %s" % ex}
+
+    line = {"metric": "AWFL dycore cell-updates/sec", "value": value, "unit": "cell-updates/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": args.workload + ": " + w["desc"], "nens_global": nens_global, "crm_dt": CRM_DT,
+                       "ncycles": cyc[-1], "cell_updates_per_step": float(ncell) * cyc[-1] * world,
+                       "l2": "inputs larger than L2: %d fields x %.0f MB per GPU, no flush needed" % (len(names), 8 * ncell / 1e6),
+                       "parallelism": "ensemble-sharded x%d, no data-path collective" % world},
+            "e2e": e2e, "gpu_launches": launches, "clocks": clocks, "roofline": roof, "whole_step": whole, "kernels": kernels,
+            "cpu_baseline": cpu_baseline, "mass_drift_rel": mass_drift}
+    print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,128 @@
+/* awfl_b200.h -- C ABI of the B200-native AWFL dycore time step (libawfl_b200.so).
+ *
+ * Drop-in boundary for ONE hot path of E3SM-Project/PAM: the AWFL dynamical-core time step
+ * (reference: dynamics/awfl/Dycore.h, class Dycore). Every entry point below replaces one public method
+ * of the reference's `class Dycore` (header-only C++ over YAKL parallel_for); the C++ shim in
+ * pam_b200/cxx/Dycore.h keeps the reference's method names and pulls raw device pointers out of the
+ * coupler's DataManager to call these. No torch / YAKL types cross this boundary: plain pointers and sizes.
+ *
+ * Conventions
+ *   - all field pointers are DEVICE pointers to FP64 arrays of shape (nz,ny,nx,nens), C order, nens fastest
+ *     (pam_core/pam_const.h:30-37, pam_core/pam_coupler.h:255-263) unless a parameter says "host";
+ *   - every function returns 0 on success, non-zero on error; awfl_last_error() gives the message
+ *     (the reference throws std::string through endrun(), pam_core/pam_const.h:249-252; the shim converts);
+ *   - a handle is bound to one device and one stream and is not thread-safe (one coupler per host thread in
+ *     the reference, pam_core/pam_interface/pam_interface.h:16-32);
+ *   - there is no CPU fallback: every entry point launches sm_100a kernels or fails.
+ */
+#ifndef AWFL_B200_H
+#define AWFL_B200_H
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct awfl_handle awfl_handle;
+
+/* Options resolved once by Dycore::init (dynamics/awfl/Dycore.h:866-981) + grid (pam_coupler.h:184-202). */
+typedef struct {
+  int nz, ny, nx, nens;          /* coupler.get_nz/ny/nx/nens                                        */
+  int num_tracers;               /* coupler.get_num_tracers()                                        */
+  int ord;                       /* reconstruction order: 3,5,7,9 (the reference's compile-time MW_ORD, Dycore.h:17-21) */
+  double xlen, ylen;             /* domain lengths [m]; dx = xlen/nx, dy = ylen/ny                   */
+  double R_d, cp_d, R_v, cp_v, p0, grav; /* Dycore.h:871-876 (defaults 287,1003,461,1859,1e5,9.81)   */
+  double gamma_d, kappa_d, C0;   /* Dycore.h:885-891; pass 0 to have them derived from the above     */
+  int idWV;                      /* index of "water_vapor" among the tracers (Dycore.h:974)          */
+  const unsigned char *tracer_positive;  /* host, num_tracers flags (Dycore.h:968)                   */
+  const unsigned char *tracer_adds_mass; /* host, num_tracers flags (Dycore.h:969)                   */
+  const double *dz_host;         /* host copy of "vertical_cell_dz" (nz,nens)                        */
+  int device;                    /* CUDA device ordinal                                              */
+  void *stream;                  /* cudaStream_t to enqueue on (NULL = the legacy default stream)       */
+} awfl_config;
+
+/* The coupler's prognostic fields (pam_coupler.h:259-263 + every registered tracer). */
+typedef struct {
+  double *density_dry, *uvel, *vvel, *wvel, *temp;
+  double *const *tracers;        /* host array of num_tracers device pointers                        */
+} awfl_fields;
+
+/* Optional large-scale columns for declare_hydrostatic(use_gcm_data=true) (Dycore.h:1416-1420), each (nz,nens) */
+typedef struct {
+  const double *gcm_density_dry, *gcm_temp, *gcm_water_vapor, *gcm_cloud_water, *gcm_cloud_ice;
+} awfl_gcm_columns;
+
+/* Dycore::init (Dycore.h:835-1091): resolves constants, builds the per-level vertical WENO matrices on the host
+ * by the reference's algorithm (Dycore.h:897-939, TransformMatrices_variable.h:10-69), uploads them, allocates
+ * the persistent workspace (no allocation happens inside a time step). */
+int awfl_create(const awfl_config *cfg, awfl_handle **out);
+
+/* Dycore::finalize (Dycore.h:1548) + destructor. Never frees caller-owned fields. */
+void awfl_destroy(awfl_handle *h);
+
+/* Message of the last failing call on this handle (or of awfl_create when h == NULL). */
+const char *awfl_last_error(const awfl_handle *h);
+
+/* Dycore::dycore_name (Dycore.h:1544). */
+const char *awfl_dycore_name(void);
+
+/* Dycore::timeStep (Dycore.h:107-255): coupler -> dycore state, clip tracers, CFL dt, ncycles SSPRK3 sub-cycles,
+ * dycore state -> coupler. Fields are updated in place. ncycles_override > 0 fixes the sub-cycle count and
+ * removes the only host sync (the 8-byte dt read-back); ncycles_out (may be NULL) receives the count used. */
+int awfl_time_step(awfl_handle *h, const awfl_fields *f, double crm_dt, int ncycles_override, int *ncycles_out);
+
+/* Same step through HOST buffers (pageable or pinned): copies the 5+num_tracers fields to the device, steps,
+ * copies them back -- the end-to-end path of a caller whose coupler lives in host memory. host_fields[0..4] =
+ * density_dry,uvel,vvel,wvel,temp, then the tracers. */
+int awfl_time_step_host(awfl_handle *h, double *const *host_fields, double crm_dt, int ncycles_override, int *ncycles_out);
+
+/* Dycore::compute_time_step (Dycore.h:65-102): min over cells of cfl*d/(|vel|+cs); result written to *dt_host. */
+int awfl_compute_time_step(awfl_handle *h, const awfl_fields *f, double cfl, double *dt_host);
+
+/* Dycore::compute_tendencies (Dycore.h:262-586) on UN-haloed conserved arrays, for tendency-level parity tests.
+ * state (5,nz,ny,nx,nens) = rho, rho*u, rho*v, rho*w, rho*theta; tracers / fct_start (num_tracers,...);
+ * outputs state_tend (5,...) and tracers_tend (num_tracers,...). All device pointers. Inputs are not modified. */
+int awfl_compute_tendencies(awfl_handle *h, const double *state, const double *tracers, const double *fct_start,
+                            double dt, double *state_tend, double *tracers_tend);
+
+/* Dycore::declare_current_profile_as_hydrostatic (Dycore.h:1392-1504), grav_balance branch: fills the handle's
+ * "variable_gravity" (nz,nens). gcm == NULL <=> use_gcm_data == false. Deterministic (no atomics). */
+int awfl_declare_hydrostatic(awfl_handle *h, const awfl_fields *f, const awfl_gcm_columns *gcm);
+
+/* Dycore::compute_mass (Dycore.h:37-60): out_host[(num_tracers+2)*nens] = mean over cells of q*dz for each tracer,
+ * rho and rho*theta. */
+int awfl_compute_mass(awfl_handle *h, const awfl_fields *f, double *out_host);
+
+/* Dycore-owned DataManager entries other modules may read (Dycore.h:868,897-898): device pointers owned by the
+ * handle. variable_gravity (nz,nens); vert_sten_to_coefs (nz+2,ord,ord,nens); vert_weno_recon_lower
+ * (nz+2,hs,hs,hs,nens) with hs=(ord+1)/2. */
+double *awfl_variable_gravity(awfl_handle *h);
+const double *awfl_vert_sten_to_coefs(awfl_handle *h);
+const double *awfl_vert_weno_recon_lower(awfl_handle *h);
+
+/* Resolved option value by name ("R_d","cp_d","R_v","cp_v","p0","grav","cv_d","gamma_d","kappa_d","C0"); NaN if unknown. */
+double awfl_get_option(const awfl_handle *h, const char *name);
+
+/* Table-level test hook for Dycore::reconstruct (Dycore.h:591-604) on the device: n stencils of `ord` values
+ * (device), ind = 0 left edge / 1 right edge. level < 0: constant horizontal matrices; else the vertical matrices
+ * of (level, iens). Static: needs no handle state besides the tables. */
+int awfl_reconstruct(awfl_handle *h, const double *stencils, int n, int ind, int level, int iens, double *out);
+
+/* Number of kernel launches issued by this handle since creation (bench.py reports the per-step count). */
+long awfl_launch_count(const awfl_handle *h);
+
+/* Per-kernel-class device timing with CUDA events on the handle's stream. Between begin and end every kernel launch is
+ * bracketed by an event pair; end synchronises and returns, per class, the summed milliseconds and the launch count.
+ * Classes (AWFL_KC_COUNT entries): */
+enum { AWFL_KC_IN = 0, AWFL_KC_OUT, AWFL_KC_STATE_X, AWFL_KC_STATE_Y, AWFL_KC_STATE_Z, AWFL_KC_TRACER_X, AWFL_KC_TRACER_Y,
+       AWFL_KC_TRACER_Z, AWFL_KC_FCT, AWFL_KC_TRACER_UPD, AWFL_KC_OTHER, AWFL_KC_COUNT };
+int awfl_profile_begin(awfl_handle *h);
+int awfl_profile_end(awfl_handle *h, double *ms_by_class, long *launches_by_class);
+
+/* FP64 FMA-pipe microbenchmark: runs `iters` dependent-chain DFMA rounds on every SM and returns the achieved
+ * TFLOP/s (2 flops per FMA) in *tflops -- the measured denominator of the FP64 roofline. */
+int awfl_measure_fp64_peak(awfl_handle *h, int iters, double *tflops);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

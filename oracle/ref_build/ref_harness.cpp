@@ -79,6 +79,15 @@ extern "C" {
 
 int ref_ord() { return ORD; }
 
+// Finalise YAKL quietly: its pool destructor otherwise prints high-water statistics to stdout at process exit,
+// which would follow bench.py's single JSON line.
+void ref_shutdown() {
+  if (yakl::isInitialized()) {
+    CoutSilencer s;
+    yakl::finalize();
+  }
+}
+
 int ref_openmp() {
   #ifdef YAKL_ARCH_OPENMP
     return 1;

@@ -4,6 +4,7 @@ reference AWFL dycore (E3SM-Project/PAM @ 58b3e77) behind oracle/ref_build/ref_h
 Only tests/, tools that generate tests/golden/, __graft_entry__.smoke() and bench.py's CPU-baseline legs
 may import this module. The product path (pam_b200/) never does.
 """
+import atexit
 import ctypes as C
 import os
 import numpy as np
@@ -61,6 +62,8 @@ def load(ord=5, omp=False):
     lib.ref_compute_mass.argtypes = [C.c_void_p, _dp]
     lib.ref_time_steps_raw.restype = C.c_double
     lib.ref_time_steps_raw.argtypes = [C.c_void_p, C.c_int]
+    lib.ref_shutdown.restype = None
+    atexit.register(lib.ref_shutdown)
     _libs[key] = lib
     return lib
 

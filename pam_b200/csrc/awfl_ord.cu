@@ -1,0 +1,53 @@
+// One translation unit per reconstruction order (-DAWFL_ORD_INST=3|5|7|9): instantiates the order-templated kernels of
+// awfl_sweep.cuh and defines the host launchers declared in awfl_types.h.
+#include "awfl_sweep.cuh"
+
+#ifndef AWFL_ORD_INST
+#error "compile with -DAWFL_ORD_INST=3|5|7|9"
+#endif
+
+namespace awfl {
+
+template <int ORD>
+void OrdLaunch<ORD>::state_sweep(cudaStream_t s, const Geom &g, const Phys &ph, const SweepArgs &a, int dir, int mode, bool shared, long items) {
+  const unsigned blocks = (unsigned)((items + WPB - 1) / WPB);
+  // x and y sweeps only ever accumulate (MODE 0); the z sweep is always the last of a stage (MODE 1 or 2)
+  if (dir == 0) k_sweep_state<ORD, 0, 0, false><<<blocks, 32 * WPB, 0, s>>>(g, ph, a);
+  else if (dir == 1) k_sweep_state<ORD, 1, 0, false><<<blocks, 32 * WPB, 0, s>>>(g, ph, a);
+  else if (mode == 1) {
+    if (shared) k_sweep_state<ORD, 2, 1, true><<<blocks, 32 * WPB, 0, s>>>(g, ph, a);
+    else k_sweep_state<ORD, 2, 1, false><<<blocks, 32 * WPB, 0, s>>>(g, ph, a);
+  } else {
+    if (shared) k_sweep_state<ORD, 2, 2, true><<<blocks, 32 * WPB, 0, s>>>(g, ph, a);
+    else k_sweep_state<ORD, 2, 2, false><<<blocks, 32 * WPB, 0, s>>>(g, ph, a);
+  }
+}
+
+template <int ORD>
+void OrdLaunch<ORD>::tracer_sweep(cudaStream_t s, const Geom &g, const TracerSweepArgs &a, int dir, bool shared, long items) {
+  const unsigned blocks = (unsigned)((items + WPB - 1) / WPB);
+  if (dir == 0) k_sweep_tracer<ORD, 0, false><<<blocks, 32 * WPB, 0, s>>>(g, a);
+  else if (dir == 1) k_sweep_tracer<ORD, 1, false><<<blocks, 32 * WPB, 0, s>>>(g, a);
+  else if (shared) k_sweep_tracer<ORD, 2, true><<<blocks, 32 * WPB, 0, s>>>(g, a);
+  else k_sweep_tracer<ORD, 2, false><<<blocks, 32 * WPB, 0, s>>>(g, a);
+}
+
+template <int ORD>
+void OrdLaunch<ORD>::hydro_pint(cudaStream_t s, const Geom &g, const Phys &ph, const HydroArgs &a, bool shared) {
+  const long ncol = (long)g.ny * g.nx * g.nens;
+  const unsigned blocks = (unsigned)((ncol + 127) / 128);
+  if (shared) k_hydro_pint<ORD, true><<<blocks, 128, 0, s>>>(g, ph, a);
+  else k_hydro_pint<ORD, false><<<blocks, 128, 0, s>>>(g, ph, a);
+}
+
+template <int ORD>
+void OrdLaunch<ORD>::reconstruct(cudaStream_t s, const double *st, int n, int ind, int level, int iens, int nens, const double *vtab,
+                                 bool shared, double *out) {
+  const unsigned blocks = (unsigned)((n + 127) / 128);
+  if (shared) k_reconstruct<ORD, true><<<blocks, 128, 0, s>>>(st, n, ind, level, iens, nens, vtab, out);
+  else k_reconstruct<ORD, false><<<blocks, 128, 0, s>>>(st, n, ind, level, iens, nens, vtab, out);
+}
+
+template struct OrdLaunch<AWFL_ORD_INST>;
+
+}  // namespace awfl

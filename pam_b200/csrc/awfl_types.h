@@ -1,0 +1,62 @@
+// Plain structs shared by the per-order kernel translation units and the host side.
+#pragma once
+#include <cuda_runtime.h>
+
+namespace awfl {
+
+enum { idR = 0, idU = 1, idV = 2, idW = 3, idT = 4, NS = 5 };
+static constexpr int WPB = 4;  // warps (work items) per block of the sweep kernels; lane = ensemble member
+
+struct Geom {
+  int nz, ny, nx, nens, nt;
+  int sim2d;
+  long ncell;     // nz*ny*nx*nens
+  double dx, dy;
+};
+struct Phys {
+  double R_d, R_v, C0, gamma, grav;
+};
+
+// State sweep arguments (k_sweep_state)
+struct SweepArgs {
+  const double *qin;      // stage input, N fields
+  const double *qbase;    // step-start state (MODE 1, a != 0)
+  double *qout;           // stage output (MODE 1) or total tendency (MODE 2), 5 fields
+  double *tend;           // partial tendencies, 5 fields
+  double *mflux;          // interface mass flux of this direction
+  const double *dz;       // (nz,nens)
+  const double *grav_var; // (nz,nens)
+  const double *vtab;     // vertical matrices
+  double a, b, c;         // SSPRK3 stage coefficients (c = b*dt)
+  int first;              // 1: this is the first sweep of the stage (tend is written, not accumulated)
+  int nseg;
+};
+
+// Tracer sweep arguments (k_sweep_tracer)
+struct TracerSweepArgs {
+  const double *qin;    // stage input, N fields (rho = field 0, tracers from field 5)
+  const double *mflux;  // interface mass flux of this direction
+  double *tflux;        // nt fields of interface fluxes for this direction
+  const double *vtab;
+  int nseg;
+  long items_per_tracer;
+};
+
+// declare_current_profile_as_hydrostatic arguments
+struct HydroArgs {
+  const double *q;        // dycore state (rho, ..., rho*theta) or NULL when gcm columns are used
+  const double *g_rd, *g_t, *g_rv, *g_rc, *g_ri;
+  const double *dz, *vtab;
+  double *pint;           // (nz+1,ny,nx,nens)
+  double *grav_var;
+};
+
+// Per-order launchers, defined in awfl_ord.cu (one translation unit per reconstruction order so they build in parallel).
+template <int ORD> struct OrdLaunch {
+  static void state_sweep(cudaStream_t s, const Geom &g, const Phys &ph, const SweepArgs &a, int dir, int mode, bool shared, long items);
+  static void tracer_sweep(cudaStream_t s, const Geom &g, const TracerSweepArgs &a, int dir, bool shared, long items);
+  static void hydro_pint(cudaStream_t s, const Geom &g, const Phys &ph, const HydroArgs &a, bool shared);
+  static void reconstruct(cudaStream_t s, const double *st, int n, int ind, int level, int iens, int nens, const double *vtab, bool shared, double *out);
+};
+
+}  // namespace awfl

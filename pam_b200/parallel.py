@@ -1,0 +1,43 @@
+"""Ensemble sharding across the GPUs of one node and the global diagnostics that go with it.
+
+The AWFL step has no data-path exchange between ranks: every stencil runs along k, j or i at a FIXED ensemble member
+(SURVEY.md 8e), so each rank owns a contiguous slab of members with its own coupler + handle -- the way E3SM-MMF places
+a fixed number of CRMs per MPI rank. The only collective is the global mass/energy diagnostic, the multi-GPU form of
+Dycore::compute_mass (dynamics/awfl/Dycore.h:37-60): one all-reduce of (num_tracers+2) doubles (NCCL on GPUs, gloo in
+the CPU tests).
+"""
+import numpy as np
+import torch
+import torch.distributed as dist
+
+
+def shard_range(nens_global, rank, world):
+    """Contiguous member slab [e0, e1) of `rank`; slabs differ by at most one member and cover [0, nens_global)."""
+    if not (0 <= rank < world):
+        raise ValueError("rank %d outside world of %d" % (rank, world))
+    base, rem = divmod(int(nens_global), int(world))
+    e0 = rank * base + min(rank, rem)
+    return e0, e0 + base + (1 if rank < rem else 0)
+
+
+def global_mass(local_mass, nens_global, group=None, device=None):
+    """local_mass: (nvars, nens_local) per-member means of q*dz (Dycore::compute_mass). Returns the (nvars,) ensemble
+    means over ALL ranks' members: sum over local members, all-reduce(SUM), divide by the global member count."""
+    lm = np.asarray(local_mass, dtype=np.float64)
+    s = torch.from_numpy(lm.sum(axis=1).copy())
+    if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+        if dist.get_backend(group) == "nccl":
+            s = s.to(device if device is not None else torch.device("cuda", torch.cuda.current_device()))
+        dist.all_reduce(s, op=dist.ReduceOp.SUM, group=group)
+    return (s.cpu().numpy()) / float(nens_global)
+
+
+def global_min_dt(local_dt, group=None, device=None):
+    """Optional uniform sub-cycle count across ranks: min of the per-rank CFL time steps (each rank of the reference
+    computes its own, Dycore.h:141; benchmarks may want one)."""
+    t = torch.tensor([float(local_dt)], dtype=torch.float64)
+    if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+        if dist.get_backend(group) == "nccl":
+            t = t.to(device if device is not None else torch.device("cuda", torch.cuda.current_device()))
+        dist.all_reduce(t, op=dist.ReduceOp.MIN, group=group)
+    return float(t.item())

@@ -1,0 +1,204 @@
+"""GPU parity tests proper: the CUDA path, called through the C ABI (pam_b200.Dycore -> libawfl_b200.so), against the
+plain-C oracle (oracle/awfl_oracle.c, itself pinned bit-for-bit to the compiled reference) on the same seeded inputs.
+
+Tolerances (FP64, BASELINE.json north_star): relative L2 of every prognostic field <= 1e-12 after one step and
+<= 1e-9 after 100 steps; dry mass conserved to round-off. Norm floors are stated in conftest.field_floors.
+"""
+import numpy as np
+import pytest
+
+from conftest import rel_l2, field_floors
+import helpers as H
+from pam_b200 import synthetic as syn
+
+pytestmark = pytest.mark.gpu
+
+TOL_STEP = 1e-12
+TOL_100 = 1e-9
+
+
+def _case(nz=16, ny=1, nx=20, nens=40, nt=1, grid="tanh", per_ens=False, seed=12345):
+    tr = syn.TRACERS_NT1 if nt == 1 else syn.TRACERS_P3_SHOC
+    return syn.make_case(nz, ny, nx, nens, tracers=tr, grid=grid, per_ens_grid=per_ens, seed=seed)
+
+
+@pytest.mark.parametrize("ord", [3, 5, 7, 9])
+def test_reconstruct_matches_oracle(ord):
+    import torch
+    case = _case(nz=12, nx=12, nens=4)
+    o = H.make_oracle(case, ord)
+    c, d = H.make_gpu(case, ord)
+    rng = np.random.default_rng(7)
+    n = 4096
+    st = rng.standard_normal((n, ord)) * np.exp(rng.uniform(-3, 3, (n, 1))) + rng.uniform(-5, 5, (n, 1))
+    st[:64] = 1.0                      # constant stencils: TV == 0 branch
+    st[64:128] = np.where(np.arange(ord) < ord // 2, 0.0, 1.0)   # step
+    st[128:192] *= 1e8                 # number-concentration magnitudes: eps in convexify matters (WenoLimiter.h:23-29)
+    dev = torch.from_numpy(st).to(c.device)
+    scale = np.abs(st).max(axis=1) + 1e-300
+    for ind in (0, 1):
+        ref = o.reconstruct(st, ind)
+        got = d.reconstruct(dev, ind).cpu().numpy()
+        assert np.max(np.abs(got - ref) / scale) < 5e-14
+        for level in (0, 1, 5, case["nz"] + 1):
+            ref = o.reconstruct_vert(level, 1, st, ind)
+            got = d.reconstruct(dev, ind, level=level, iens=1).cpu().numpy()
+            assert np.max(np.abs(got - ref) / scale) < 5e-13
+
+
+def test_vertical_tables_and_options_match_oracle():
+    case = _case(per_ens=True)
+    o = H.make_oracle(case)
+    c, d = H.make_gpu(case)
+    dm = c.get_data_manager_device_readonly()
+    vt = o.vert_tables()
+    assert np.array_equal(dm.get("vert_sten_to_coefs").cpu().numpy(), vt["vert_sten_to_coefs"])
+    assert np.array_equal(dm.get("vert_weno_recon_lower").cpu().numpy(), vt["vert_weno_recon_lower"])
+    for k in ("R_d", "cp_d", "R_v", "cp_v", "p0", "grav", "cv_d", "gamma_d", "kappa_d", "C0"):
+        assert c.get_option(k) == o.option(k)
+    assert d.dycore_name() == "SSPRK3+WENO+FV A-grid"
+
+
+@pytest.mark.parametrize("cfg", [
+    dict(),                                    # 2-D, NT=1, ragged nens (40 = 32 + 8)
+    dict(per_ens=True),                        # member-dependent vertical grid (general matrix path)
+    dict(ny=6, nx=8, nz=10, nens=33),          # 3-D
+    dict(nt=10, nens=32),                      # P3+SHOC tracer set, FCT triggers
+    dict(grid="equal", nens=1),                # single member
+])
+def test_tendencies_match_oracle(cfg):
+    import torch
+    case = _case(**cfg)
+    o = H.make_oracle(case)
+    c, d = H.make_gpu(case)
+    o.declare_hydrostatic()
+    d.declare_current_profile_as_hydrostatic(c)
+    g_ref = o.get_field("variable_gravity")
+    g_got = c.get_data_manager_device_readonly().get("variable_gravity").cpu().numpy()
+    assert rel_l2(g_got, g_ref) < 1e-11     # residual of two ~1e5 Pa reconstructions divided by rho*dz
+    o.set_variable_gravity(g_got)           # same gravity on both sides for the tendency comparison
+    # conserved state from the oracle's own conversion: run a zero-length trick -> use numpy restatement
+    f = case["fields"]
+    R_d, R_v, C0, gamma = o.option("R_d"), o.option("R_v"), o.option("C0"), o.option("gamma_d")
+    names = [t[0] for t in case["tracers"]]
+    rho = f["density_dry"].copy()
+    for (n, pos, adds) in case["tracers"]:
+        if adds:
+            rho = rho + f[n]
+    press = f["density_dry"] * R_d * f["temp"] + f["water_vapor"] * R_v * f["temp"]
+    theta = np.power(press / C0, 1.0 / gamma) / rho
+    state = np.stack([rho, rho * f["uvel"], rho * f["vvel"], rho * f["wvel"], rho * theta])
+    tracers = np.stack([np.maximum(f[n], 0.0) for n in names])
+    dt = 0.7
+    st_ref, tt_ref, _, _ = o.compute_tendencies(state, tracers, tracers, dt)
+    st_got, tt_got = d.compute_tendencies(torch.from_numpy(state).to(c.device), torch.from_numpy(tracers).to(c.device),
+                                          torch.from_numpy(tracers).to(c.device), dt)
+    st_got, tt_got = st_got.cpu().numpy(), tt_got.cpu().numpy()
+    # tendencies are differences of fluxes: normalise by the flux scale |F|/d rather than by the (possibly ~0) tendency
+    for l in range(5):
+        scale = max(np.linalg.norm(st_ref[l]), 1e-6 * np.linalg.norm(st_ref[0]) * 350.0)
+        assert np.linalg.norm(st_got[l] - st_ref[l]) / scale < 1e-11, l
+    for t in range(len(names)):
+        scale = max(np.linalg.norm(tt_ref[t]), 1e-12 * np.linalg.norm(tracers[t]))
+        assert np.linalg.norm(tt_got[t] - tt_ref[t]) / max(scale, 1e-300) < 1e-10, names[t]
+
+
+@pytest.mark.parametrize("cfg", [
+    dict(ord=5),
+    dict(ord=5, per_ens=True),
+    dict(ord=5, ny=6, nx=8, nz=10, nens=33),
+    dict(ord=5, nt=10, nens=32),
+    dict(ord=3), dict(ord=7), dict(ord=9, nz=12),
+])
+def test_one_step_matches_oracle(cfg):
+    cfg = dict(cfg)
+    ord = cfg.pop("ord")
+    case = _case(**cfg)
+    o = H.make_oracle(case, ord, crm_dt=2.0)
+    c, d = H.make_gpu(case, ord, crm_dt=2.0)
+    o.declare_hydrostatic()
+    d.declare_current_profile_as_hydrostatic(c)
+    assert abs(d.compute_time_step(c) / o.compute_time_step() - 1.0) < 1e-14
+    n_ref = o.time_step()
+    n_got = d.timeStep(c)
+    assert n_ref == n_got
+    ref, got = o.get_fields(), H.gpu_fields(c)
+    fl = field_floors(ref)
+    for k in ref:
+        assert rel_l2(got[k], ref[k], fl[k]) <= TOL_STEP, (k, rel_l2(got[k], ref[k], fl[k]))
+    # Dycore::compute_mass parity and tracer positivity
+    m_ref, m_got = o.compute_mass(), d.compute_mass(c)
+    assert np.max(np.abs(m_got - m_ref) / (np.abs(m_ref) + 1e-300)) < 1e-12
+    for (n, pos, adds) in case["tracers"]:
+        if pos:
+            assert got[n].min() >= 0.0
+
+
+def test_hundred_steps_match_oracle_and_conserve_mass():
+    case = _case(nz=12, nx=12, nens=8)
+    o = H.make_oracle(case, 5, crm_dt=1.0)
+    c, d = H.make_gpu(case, 5, crm_dt=1.0)
+    o.declare_hydrostatic()
+    d.declare_current_profile_as_hydrostatic(c)
+    m0 = d.compute_mass(c)
+    for _ in range(100):
+        o.time_step()
+        d.timeStep(c)
+    ref, got = o.get_fields(), H.gpu_fields(c)
+    fl = field_floors(ref)
+    for k in ref:
+        assert rel_l2(got[k], ref[k], fl[k]) <= TOL_100, (k, rel_l2(got[k], ref[k], fl[k]))
+    m1 = d.compute_mass(c)
+    nt = len(case["tracers"])
+    # total mass (rho*dz mean, row nt) to round-off: 100 steps x 3 stages of FP64 sums
+    assert np.max(np.abs(m1[nt] - m0[nt]) / np.abs(m0[nt])) < 1e-13
+    # dry mass = total - sum(adds_mass tracers)
+    dry0 = m0[nt] - sum(m0[i] for i, t in enumerate(case["tracers"]) if t[2])
+    dry1 = m1[nt] - sum(m1[i] for i, t in enumerate(case["tracers"]) if t[2])
+    assert np.max(np.abs(dry1 - dry0) / np.abs(dry0)) < 1e-13
+
+
+def test_use_gcm_columns_hydrostatic():
+    import torch
+    case = _case(nens=5)
+    o = H.make_oracle(case)
+    c, d = H.make_gpu(case)
+    nz, nens = case["nz"], case["nens"]
+    f = case["fields"]
+    cols = {"gcm_density_dry": f["density_dry"].mean(axis=(1, 2)), "gcm_temp": f["temp"].mean(axis=(1, 2)),
+            "gcm_water_vapor": f["water_vapor"].mean(axis=(1, 2)), "gcm_cloud_water": np.full((nz, nens), 1e-5),
+            "gcm_cloud_ice": np.full((nz, nens), 2e-6)}
+    dm = c.get_data_manager_device_readwrite()
+    for k, v in cols.items():
+        o.set_field(k, v)
+        dm.get(k).copy_(torch.from_numpy(np.ascontiguousarray(v)))
+    o.declare_hydrostatic(use_gcm=True)
+    d.declare_current_profile_as_hydrostatic(c, use_gcm_data=True)
+    assert rel_l2(dm.get("variable_gravity").cpu().numpy(), o.get_field("variable_gravity")) < 1e-11
+
+
+def test_fixed_ncycles_and_host_buffer_entry_point_agree():
+    case = _case(nens=7)
+    c, d = H.make_gpu(case, 5, crm_dt=2.0)
+    d.declare_current_profile_as_hydrostatic(c)
+    names = list(H.STATE_FIELDS) + c.get_tracer_names()
+    host = [np.ascontiguousarray(case["fields"][n]).copy() for n in names]
+    n1 = d.timeStep(c)
+    n2 = d.time_step_host(host, 2.0, ncycles=n1)
+    assert n1 == n2
+    got = H.gpu_fields(c)
+    for n, a in zip(names, host):
+        assert np.array_equal(a, got[n]), n      # same kernels, same inputs: bit-identical
+
+
+def test_errors_are_reported_not_swallowed():
+    from pam_b200 import PamCoupler, Dycore
+    c = PamCoupler("cuda:0")
+    c.set_option("crm_dt", 1.0)
+    c.allocate_coupler_state(8, 1, 8, 2)
+    c.set_grid(8000.0, 1000.0, np.arange(9) * 100.0)
+    c.add_tracer("cloud_water", "", True, True)   # no water_vapor
+    with pytest.raises(RuntimeError):
+        Dycore(5).init(c)
+    with pytest.raises(RuntimeError):
+        Dycore(4)

@@ -315,7 +315,10 @@ struct awfl_handle {
   double *mflux[3];      // x,y (ncell), z (ncell + one level)
   double *tflux[3];      // nt fields each
   double *mult;          // nt fields
-  double *dz, *grav_var, *vtab, *vs2c, *vwrl, *pint;
+  double *dz, *rdz, *grav_var, *vtab, *vs2c, *vwrl, *pint;
+  std::vector<double> vtab_h;   // host copy of the kernel table (constant-bank upload)
+  bool use_cvtab;               // shared vertical grid whose table fits the constant bank
+  bool sweep_v1;                // AWFL_SWEEP=v1: the register-window sweep kernels (kept for A/B measurements)
   double *dt_min_d, *dt_min_h;   // device scalar + pinned host scalar
   double *mass_d;
   unsigned char *positive_d, *adds_mass_d;
@@ -331,6 +334,9 @@ struct awfl_handle {
 };
 
 static std::string g_create_err;
+// The constant-bank copy of the vertical matrices is per process and per reconstruction order: remember whose it is.
+static const awfl_handle *g_cvtab_owner[4] = {nullptr, nullptr, nullptr, nullptr};
+static int ord_slot(int ord) { return (ord - 3) / 2; }
 
 #define CK(call)                                                                                        \
   do {                                                                                                  \
@@ -473,10 +479,31 @@ static long items_for(const awfl_handle *h, int dir, int nseg) {
     default: OrdLaunch<9>::CALL; break;          \
   }
 
+// Make sure the constant-bank table belongs to this handle before a z march reads it. Another handle of the same
+// order may have replaced it; its kernels may still be running on another stream, so a change of owner synchronises
+// the device first (never happens with one handle per device and order, the normal case).
+static int ensure_cvtab(awfl_handle *h) {
+  if (!h->use_cvtab || h->sweep_v1) return 0;
+  const int slot = ord_slot(h->ord);
+  if (g_cvtab_owner[slot] == h) return 0;
+  if (g_cvtab_owner[slot] != nullptr) CK(cudaDeviceSynchronize());
+  int rc = 0;
+  switch (h->ord) {
+    case 3: rc = OrdLaunch<3>::upload_cvtab(h->stream, h->vtab_h.data(), h->vtab_h.size()); break;
+    case 5: rc = OrdLaunch<5>::upload_cvtab(h->stream, h->vtab_h.data(), h->vtab_h.size()); break;
+    case 7: rc = OrdLaunch<7>::upload_cvtab(h->stream, h->vtab_h.data(), h->vtab_h.size()); break;
+    default: rc = OrdLaunch<9>::upload_cvtab(h->stream, h->vtab_h.data(), h->vtab_h.size()); break;
+  }
+  if (rc != 0) return fail(h, std::string("constant-bank upload of the vertical matrices: ") + cudaGetErrorString((cudaError_t)rc));
+  g_cvtab_owner[slot] = h;
+  return 0;
+}
+
 static void launch_state_sweep(awfl_handle *h, int dir, int mode, const SweepArgs &a) {
   const long items = items_for(h, dir, a.nseg);
   ProfScope ps(h, KC_STATE_X + dir);
-  AWFL_ORD_DISPATCH(state_sweep(h->stream, h->g, h->ph, a, dir, mode, h->shared_grid, items));
+  if (h->sweep_v1) { AWFL_ORD_DISPATCH(state_sweep(h->stream, h->g, h->ph, a, dir, mode, h->shared_grid, items)); }
+  else { AWFL_ORD_DISPATCH(march_state(h->stream, h->g, h->ph, a, dir, mode, dir == 2 ? (h->use_cvtab ? 1 : 2) : 0, items)); }
 }
 
 static void launch_tracer_sweep(awfl_handle *h, int dir, TracerSweepArgs a) {
@@ -484,7 +511,8 @@ static void launch_tracer_sweep(awfl_handle *h, int dir, TracerSweepArgs a) {
   a.items_per_tracer = items_for(h, dir, a.nseg);
   const long items = a.items_per_tracer * h->g.nt;
   ProfScope ps(h, KC_TRACER_X + dir);
-  AWFL_ORD_DISPATCH(tracer_sweep(h->stream, h->g, a, dir, h->shared_grid, items));
+  if (h->sweep_v1) { AWFL_ORD_DISPATCH(tracer_sweep(h->stream, h->g, a, dir, h->shared_grid, items)); }
+  else { AWFL_ORD_DISPATCH(march_tracer(h->stream, h->g, a, dir, dir == 2 ? (h->use_cvtab ? 1 : 2) : 0, items)); }
 }
 
 // One semi-discrete right-hand side + stage combination.
@@ -501,11 +529,11 @@ static void run_stage(awfl_handle *h, const double *qin, const double *q0, doubl
     const bool last = d == ndir - 1;
     SweepArgs s;
     s.qin = qin; s.qbase = q0; s.qout = mode == 2 ? st_out : qout; s.tend = h->tend; s.mflux = h->mflux[dir];
-    s.dz = h->dz; s.grav_var = h->grav_var; s.vtab = h->vtab;
+    s.dz = h->dz; s.grav_var = h->grav_var; s.vtab = h->vtab; s.rdz = h->rdz; s.vst = h->shared_grid ? 1 : g.nens;
     s.a = a; s.b = b; s.c = b * dt_full; s.first = d == 0; s.nseg = nseg_for(h, nn[dir]);
     launch_state_sweep(h, dir, last ? mode : 0, s);
     TracerSweepArgs t;
-    t.qin = qin; t.mflux = h->mflux[dir]; t.tflux = h->tflux[dir]; t.vtab = h->vtab; t.nseg = s.nseg; t.items_per_tracer = 0;
+    t.qin = qin; t.mflux = h->mflux[dir]; t.tflux = h->tflux[dir]; t.vtab = h->vtab; t.vst = s.vst; t.nseg = s.nseg; t.items_per_tracer = 0;
     launch_tracer_sweep(h, dir, t);
   }
   if (g.nt > 0) {
@@ -584,6 +612,10 @@ int awfl_create(const awfl_config *cfg, awfl_handle **out) {
   if (getenv("AWFL_FORCE_PER_ENS_GRID")) h->shared_grid = false;
   std::vector<double> vs2c, vwrl, vtab;
   build_vertical(h->ord, g.nz, g.nens, cfg->dz_host, h->shared_grid, vs2c, vwrl, vtab);
+  h->sweep_v1 = false;
+  if (const char *s = getenv("AWFL_SWEEP")) h->sweep_v1 = std::string(s) == "v1";
+  h->use_cvtab = h->shared_grid && vtab.size() <= OrdLaunch<5>::cvtab_capacity() && !getenv("AWFL_NO_CVTAB");
+  if (h->use_cvtab) h->vtab_h = vtab;
   const size_t fb = sizeof(double) * (size_t)g.ncell;
   const size_t lvl = sizeof(double) * (size_t)g.ny * g.nx * g.nens;
 #define ALLOC(ptr, bytes) do { if (cudaMalloc((void **)&(ptr), (bytes)) != cudaSuccess) return bail(std::string("cudaMalloc failed for ") + #ptr); } while (0)
@@ -593,6 +625,7 @@ int awfl_create(const awfl_config *cfg, awfl_handle **out) {
   ALLOC(h->tflux[0], fb * nt); ALLOC(h->tflux[1], fb * nt); ALLOC(h->tflux[2], (fb + lvl) * nt);
   ALLOC(h->mult, fb * nt);
   ALLOC(h->dz, sizeof(double) * g.nz * g.nens);
+  ALLOC(h->rdz, sizeof(double) * g.nz * g.nens);
   ALLOC(h->grav_var, sizeof(double) * g.nz * g.nens);
   ALLOC(h->vtab, sizeof(double) * vtab.size());
   ALLOC(h->vs2c, sizeof(double) * vs2c.size());
@@ -605,6 +638,11 @@ int awfl_create(const awfl_config *cfg, awfl_handle **out) {
   h->stage_fields = nullptr; h->tmp_state = nullptr;
   if (cudaMallocHost((void **)&h->dt_min_h, sizeof(double)) != cudaSuccess) return bail("cudaMallocHost failed");
   cudaMemcpy(h->dz, cfg->dz_host, sizeof(double) * g.nz * g.nens, cudaMemcpyHostToDevice);
+  {
+    std::vector<double> rdz((size_t)g.nz * g.nens);
+    for (size_t i = 0; i < rdz.size(); i++) rdz[i] = 1.0 / cfg->dz_host[i];
+    cudaMemcpy(h->rdz, rdz.data(), sizeof(double) * rdz.size(), cudaMemcpyHostToDevice);
+  }
   cudaMemset(h->grav_var, 0, sizeof(double) * g.nz * g.nens);   // the reference leaves it uninitialised
   cudaMemcpy(h->vtab, vtab.data(), sizeof(double) * vtab.size(), cudaMemcpyHostToDevice);
   cudaMemcpy(h->vs2c, vs2c.data(), sizeof(double) * vs2c.size(), cudaMemcpyHostToDevice);
@@ -621,7 +659,8 @@ void awfl_destroy(awfl_handle *h) {
   for (int b = 0; b < 3; b++) cudaFree(h->Q[b]);
   cudaFree(h->tend);
   for (int d = 0; d < 3; d++) { cudaFree(h->mflux[d]); cudaFree(h->tflux[d]); }
-  cudaFree(h->mult); cudaFree(h->dz); cudaFree(h->grav_var); cudaFree(h->vtab); cudaFree(h->vs2c); cudaFree(h->vwrl);
+  for (int o = 0; o < 4; o++) if (g_cvtab_owner[o] == h) g_cvtab_owner[o] = nullptr;
+  cudaFree(h->mult); cudaFree(h->dz); cudaFree(h->rdz); cudaFree(h->grav_var); cudaFree(h->vtab); cudaFree(h->vs2c); cudaFree(h->vwrl);
   cudaFree(h->pint); cudaFree(h->dt_min_d); cudaFree(h->mass_d); cudaFree(h->positive_d); cudaFree(h->adds_mass_d);
   cudaFree(h->trptr_d); cudaFree(h->stage_fields); cudaFree(h->tmp_state);
   if (h->dt_min_h) cudaFreeHost(h->dt_min_h);
@@ -687,6 +726,7 @@ int awfl_time_step(awfl_handle *h, const awfl_fields *f, double crm_dt, int ncyc
     ncycles = (int)ceil(crm_dt / dt_dyn);   // Dycore.h:144
   }
   const double dt = crm_dt / ncycles;       // Dycore.h:145
+  if (ensure_cvtab(h)) return 1;
   for (int c = 0; c < ncycles; c++) {
     // SSPRK3, Dycore.h:147-222. Q0 = step state, Q1/Q2 = stage states.
     run_stage(h, h->Q[0], h->Q[0], h->Q[1], 0.0, 1.0, dt, dt, 1.0, 0.0, 1, nullptr, nullptr, nullptr);
@@ -726,6 +766,7 @@ int awfl_compute_tendencies(awfl_handle *h, const double *state, const double *t
   // gather (state | tracers) into one N-field buffer
   CK(cudaMemcpyAsync(h->Q[1], state, fb * NS, cudaMemcpyDeviceToDevice, h->stream));
   if (g.nt > 0) CK(cudaMemcpyAsync(h->Q[1] + (size_t)NS * g.ncell, tracers, fb * g.nt, cudaMemcpyDeviceToDevice, h->stream));
+  if (ensure_cvtab(h)) return 1;
   run_stage(h, h->Q[1], h->Q[1], nullptr, 0.0, 1.0, dt, dt, 1.0, 0.0, 2, fct_start, state_tend, tracers_tend);
   CK(cudaGetLastError());
   CK(cudaStreamSynchronize(h->stream));

@@ -1,0 +1,280 @@
+// Cell-centred marching sweep kernels of the AWFL time step (sm_100a). Included only by awfl_ord.cu.
+//
+// One warp = 32 consecutive ensemble members of one line segment (every global access is a coalesced 256-byte line);
+// the warp marches cell by cell along the sweep direction. The stencil window of each thread lives in a shared-memory
+// ring (one private column per thread: no bank conflicts, no barriers), which keeps the register footprint small enough
+// for 16-24 resident warps per SM -- the FP64 pipe, not latency, is then the limit (profiles/r01a: the register-window
+// kernels ran 8 warps/SM at 51 % / 33 % FP64-pipe utilisation, stalled on fixed-latency dependencies).
+//
+// Cell-centred formulation of Dycore.h:334-519: per marched cell c ONE set of WENO polynomials is built from the window
+// c-hs+1..c+hs-1 -- the acoustic pair (rho*u_n, p) and the four advected quantities (u, v, w, theta). Interface c takes
+// its left states from the saved right-edge values of cell c-1 and its right states from the left-edge values of cell
+// c; the upwind advective value is a select between the two (Dycore.h:368). All six reconstructions of a step use the
+// matrices of the same level, so the vertical per-level matrices are warp-uniform constant-bank loads.
+#pragma once
+#include <math.h>
+#include "awfl_types.h"
+#include "awfl_weno.cuh"
+
+namespace awfl {
+
+// Ring fields in marching order: the acoustic pair first, then the four advected quantities, then density.
+enum { RF_M = 0, RF_P, RF_U, RF_V, RF_W, RF_T, RF_R, RF_COUNT };
+
+template <int ORD> struct MarchCfg {
+  static constexpr int MINB = ORD == 3 ? 6 : (ORD == 5 ? 4 : (ORD == 7 ? 3 : 2));       // resident blocks per SM (state)
+  static constexpr int MINB_TR = ORD == 3 ? 8 : (ORD == 5 ? 6 : (ORD == 7 ? 4 : 3));    // resident blocks per SM (tracer)
+  // per thread: the window ring (RF_COUNT fields x ORD cells) + the previous interface's 5 fluxes + 4 right-edge values
+  static constexpr int COLS_STATE = RF_COUNT * ORD + NS + 4;
+  static constexpr size_t SMEM_STATE = (size_t)COLS_STATE * MT * sizeof(double);
+  static constexpr size_t SMEM_TRACER = (size_t)ORD * MT * sizeof(double);
+};
+
+// x^g for x > 0 (normal range): exp(g*log(x)). Relative error <~ 3e-15 for the arguments met here (|g log x| < 20),
+// against 94 FP64-pipe instructions for the correctly rounded pow(): 49. Stated in DESIGN.md (tolerance budget).
+__device__ __forceinline__ double pow_pos(double x, double g) { return exp(g * log(x)); }
+
+struct Raw { double r, ru, rv, rw, rt; };
+
+// Matrix provider of a step: VT 0 = constant horizontal tables, 1 = vertical tables in the constant bank (all members
+// share one vertical grid), 2 = vertical tables in global memory (member-dependent grid, or table too large).
+template <int ORD, int VT> struct MatSel;
+template <int ORD> struct MatSel<ORD, 0> {
+  using type = HMat<ORD>;
+  static __device__ __forceinline__ type get(const double *, long, long, int) { return type(); }
+};
+template <int ORD> struct MatSel<ORD, 1> {
+  using type = CMat<ORD>;
+  static __device__ __forceinline__ type get(const double *, long, long, int level) { type m; m.base = level * CMat<ORD>::NEL; return m; }
+};
+template <int ORD> struct MatSel<ORD, 2> {
+  using type = VMat<ORD>;
+  static __device__ __forceinline__ type get(const double *vtab, long vst, long voff, int level) {
+    type m; m.p = vtab + (long)level * VMat<ORD>::NEL * vst + voff; m.st = vst; return m;
+  }
+};
+
+// ---------------------------------------------------------------------------------------------------------------
+// State march: Dycore.h:310-321 (primitives, pressure), :629-710 (periodic wrap / wall ghost cells), :334-519 (one
+// direction of the flux kernel), :553-566 (flux divergence, gravity) and, on the last sweep of a stage, the SSPRK3
+// stage combination :162-165 / :182-187 / :206-211.
+//   MODE 0: write (first sweep) or accumulate this direction's flux divergence into tend[5]
+//   MODE 1: last sweep: finish the tendency and write qout = a*qbase + b*roundtrip(qin) + c*tend
+//   MODE 2: last sweep: finish the tendency and write it to qout (tendency-level parity entry point)
+// ---------------------------------------------------------------------------------------------------------------
+template <int ORD, int DIR, int MODE, int VT>
+__global__ void __launch_bounds__(MT, MarchCfg<ORD>::MINB)
+k_march_state(const Geom g, const Phys ph, const SweepArgs a) {
+  constexpr int HS = (ORD + 1) / 2;
+  constexpr double cs = 350.0;             // Dycore.h:335
+  constexpr double rcs = 1.0 / 350.0;
+  constexpr int NORMAL = DIR == 0 ? idU : (DIR == 1 ? idV : idW);
+  extern __shared__ double ring_smem[];
+  Item it;
+  if (!decode_item<DIR>((long)blockIdx.x * WPB + (threadIdx.x >> 5), g, a.nseg, it)) return;
+  const int n = DIR == 0 ? g.nx : (DIR == 1 ? g.ny : g.nz);
+  const long sd = stride_of(DIR, g);
+  const long nc = g.ncell;
+  const double *__restrict__ q = a.qin;
+  double *const rb = ring_smem + threadIdx.x;            // this thread's column: entry e at rb[e*MT]
+  double *const fpv = rb + (RF_COUNT * ORD) * MT;        // previous interface: fluxes [0..4], right-edge values [5..8]
+  const long voff = a.vst > 1 ? it.e : 0;
+
+  auto fetch = [&](int c) -> Raw {
+    int cw;
+    if (DIR == 2) cw = c < 0 ? 0 : (c >= n ? n - 1 : c);            // wall ghosts derive from the boundary cell
+    else cw = c < 0 ? c + n : (c >= n ? c - n : c);                 // periodic, Dycore.h:629-657
+    const long idx = it.base + (long)cw * sd;
+    Raw x;
+    x.r = __ldg(q + idx); x.ru = __ldg(q + nc + idx); x.rv = __ldg(q + 2 * nc + idx); x.rw = __ldg(q + 3 * nc + idx);
+    x.rt = __ldg(q + 4 * nc + idx);
+    return x;
+  };
+  // conserved -> primitives + pressure (Dycore.h:310-321); wall ghosts per Dycore.h:662-710 with the intended
+  // semantics of SURVEY.md F2 (ghost theta = theta of the boundary cell)
+  auto put = [&](const Raw &x, int c, int so) {
+    const double rinv = rcp_pos(x.r);
+    double r = x.r, w = x.rw * rinv;
+    double m = DIR == 0 ? x.ru : (DIR == 1 ? x.rv : x.rw);
+    double p = ph.C0 * pow_pos(x.rt, ph.gamma);
+    if (DIR == 2 && (c < 0 || c >= n)) {
+      // hydrostatic constant-theta extrapolation: rho_g^(gamma-1) = rho0^(gamma-1) +- grav (gamma-1) dz0 dist / (gamma C0 theta0^gamma)
+      // (Dycore.h:683-690, :697-704), with C0 theta0^gamma = p0 / rho0^gamma
+      const int dist = c < 0 ? -c : c - n + 1;
+      const double sgn = c < 0 ? 1.0 : -1.0;
+      const double dz0 = __ldg(a.dz + (long)(c < 0 ? 0 : n - 1) * g.nens + it.e);
+      const double A = pow_pos(x.r, ph.gamma);
+      const double coef = ph.grav * (ph.gamma - 1.0) * dz0 * A / (ph.gamma * p);
+      const double X = fma(sgn * coef, (double)dist, A * rinv);
+      const double rg = pow_pos(X, 1.0 / (ph.gamma - 1.0));
+      p = (p / A) * rg * X;            // C0 (rho_g theta0)^gamma, Dycore.h:691-694
+      r = rg; w = 0.0; m = 0.0;
+    }
+    rb[(RF_M * ORD) * MT + so] = m;
+    rb[(RF_P * ORD) * MT + so] = p;
+    rb[(RF_U * ORD) * MT + so] = x.ru * rinv;
+    rb[(RF_V * ORD) * MT + so] = x.rv * rinv;
+    rb[(RF_W * ORD) * MT + so] = w;
+    rb[(RF_T * ORD) * MT + so] = x.rt * rinv;
+    rb[(RF_R * ORD) * MT + so] = r;
+  };
+
+  int off[ORD];                       // ring offsets of the ORD most recent cells, oldest first
+#pragma unroll
+  for (int s = 0; s < ORD; s++) off[s] = s * MT;
+  const double rdd_h = DIR == 0 ? 1.0 / g.dx : 1.0 / g.dy;
+  double mL = 0.0, pL = 0.0;
+  const int jfirst = it.c0 - 1 - (HS - 1), jlast = it.c1 + HS - 1;
+  Raw cur = fetch(jfirst);
+
+#pragma unroll 1
+  for (int j = jfirst; j <= jlast; j++) {
+    Raw nxt = cur;
+    if (j < jlast) nxt = fetch(j + 1);
+    {                                  // newest cell replaces the oldest
+      const int o0 = off[0];
+      put(cur, j, o0);
+#pragma unroll
+      for (int s = 0; s < ORD - 1; s++) off[s] = off[s + 1];
+      off[ORD - 1] = o0;
+    }
+    cur = nxt;
+    const int c = j - (HS - 1);        // cell whose window c-HS+1..c+HS-1 is now complete
+    if (c < it.c0 - 1) continue;
+    const typename MatSel<ORD, VT>::type mat = MatSel<ORD, VT>::get(a.vtab, a.vst, voff, c + 1);
+    const bool flux_on = c >= it.c0;           // interface c belongs to this segment
+    const bool upd_on = c > it.c0;             // cell c-1 has both interfaces
+    const bool wall = (DIR == 2) && (c == 0 || c == n);   // Dycore.h:477,482,496
+    const int cc = c - 1;
+    const long idx = it.base + (long)cc * sd;
+    const int k = DIR == 2 ? cc : it.la;
+    double rdd = rdd_h, rho = 0.0, gv = 0.0;
+    const int so = off[HS - 2];                // ring slot of cell c-1
+    if (upd_on) {
+      if (DIR == 2) rdd = __ldg(a.rdz + (long)k * g.nens + it.e);
+      if (MODE != 0) { rho = rb[(RF_R * ORD) * MT + so]; gv = __ldg(a.grav_var + (long)k * g.nens + it.e); }
+    }
+    double mR = 0.0, mLn = 0.0, rn = 0.0, pp = 0.0;
+    bool up = false;
+    // one pass per reconstructed quantity: rho*u_n, p (acoustic pair), then u, v, w, theta
+#pragma unroll 1
+    for (int v = 0; v < 6; v++) {
+      const double *fb = rb + (v * ORD) * MT;
+      double st[ORD], E, O;
+#pragma unroll
+      for (int s = 0; s < ORD; s++) st[s] = fb[off[s]];
+      weno_EO<ORD>(st, mat, E, O);
+      if (v == 0) { mR = E - O; mLn = E + O; continue; }
+      int l;
+      double F;
+      if (v == 1) {
+        // interface c: characteristic upwinding, Dycore.h:361-365
+        const double pR = E - O;
+        if (wall) { mL = 0.0; mR = 0.0; }
+        const double w1 = 0.5 * (pR - cs * mR);
+        const double w2 = 0.5 * (pL + cs * mL);
+        pp = w1 + w2;
+        rn = wall ? 0.0 : (w2 - w1) * rcs;
+        up = rn > 0.0;                 // Dycore.h:368: the upwind cell is c-1 when the mass flux is positive
+        mL = mLn; pL = E + O;
+        // interface mass flux for the tracer march (x,y: n entries, seam stored at 0; z: n+1 entries)
+        if (flux_on && (c < it.c1 || (DIR == 2 && c == n))) a.mflux[it.base + (long)c * sd] = rn;
+        l = idR; F = rn;
+      } else {
+        l = v - 1;                     // idU..idT
+        F = rn * (up ? fpv[(NS + v - 2) * MT] : E - O);
+        fpv[(NS + v - 2) * MT] = E + O;
+        if (l == NORMAL) F += pp;
+      }
+      if (!flux_on) continue;
+      if (upd_on) {
+        const double div = (F - fpv[l * MT]) * rdd;
+        double T = a.first ? -div : a.tend[l * nc + idx] - div;
+        if (MODE == 0) a.tend[l * nc + idx] = T;
+        else {
+          if (l == idW) T = fma(-gv, rho, T);                 // Dycore.h:560
+          if (l == idV && g.sim2d) T = 0.0;                   // Dycore.h:565
+          if (MODE == 2) a.qout[l * nc + idx] = T;
+          else {
+            // round-tripped stage input (x/rho)*rho, Dycore.h:316-319 + :527-530
+            const double rt = l == idR ? rho : rb[((RF_U + l - 1) * ORD) * MT + so] * rho;
+            double o = a.b * rt;
+            if (a.a != 0.0) o = fma(a.a, a.qbase[l * nc + idx], o);   // plain load: qout may alias qbase
+            a.qout[l * nc + idx] = fma(a.c, T, o);
+          }
+        }
+      }
+      fpv[l * MT] = F;
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Tracer march: the tracer part of Dycore.h:381-385 / :434-438 / :513-517. flux = massflux * upwind WENO edge value of
+// (tracer/rho), cell-centred like the state march. Work item = (tracer, line, segment, ensemble tile).
+// ---------------------------------------------------------------------------------------------------------------
+template <int ORD, int DIR, int VT>
+__global__ void __launch_bounds__(MT, MarchCfg<ORD>::MINB_TR)
+k_march_tracer(const Geom g, const TracerSweepArgs a) {
+  constexpr int HS = (ORD + 1) / 2;
+  extern __shared__ double ring_smem[];
+  const long gitem = (long)blockIdx.x * WPB + (threadIdx.x >> 5);
+  const int tr = (int)(gitem / a.items_per_tracer);
+  if (tr >= g.nt) return;
+  Item it;
+  if (!decode_item<DIR>(gitem % a.items_per_tracer, g, a.nseg, it)) return;
+  const int n = DIR == 0 ? g.nx : (DIR == 1 ? g.ny : g.nz);
+  const long sd = stride_of(DIR, g);
+  const long nc = g.ncell;
+  const double *__restrict__ rho = a.qin;
+  const double *__restrict__ tq = a.qin + (long)(NS + tr) * nc;
+  double *__restrict__ fl = a.tflux + (long)tr * (DIR == 2 ? nc + nc / g.nz : nc);
+  double *const rb = ring_smem + threadIdx.x;
+  const long voff = a.vst > 1 ? it.e : 0;
+  auto cell_index = [&](int c) -> long {
+    int cw;
+    if (DIR == 2) cw = c < 0 ? 0 : (c >= n ? n - 1 : c);       // wall: zero-gradient mixing ratio, Dycore.h:674-677
+    else cw = c < 0 ? c + n : (c >= n ? c - n : c);            // periodic, Dycore.h:629-657
+    return it.base + (long)cw * sd;
+  };
+  int off[ORD];
+#pragma unroll
+  for (int s = 0; s < ORD; s++) off[s] = s * MT;
+  {
+    const int cs0 = it.c0 - 1 - (HS - 1);
+#pragma unroll
+    for (int s = 0; s < ORD; s++) {
+      const long idx = cell_index(cs0 + s);
+      rb[off[s]] = __ldg(tq + idx) * rcp_pos(__ldg(rho + idx));        // Dycore.h:320
+    }
+  }
+  double Rp = 0.0;
+#pragma unroll 1
+  for (int c = it.c0 - 1; c < it.c1; c++) {
+    const bool more = c + 1 < it.c1;
+    double nq = 0.0, nr = 1.0, rn = 0.0;
+    if (more) { const long idx = cell_index(c + HS); nq = __ldg(tq + idx); nr = __ldg(rho + idx); }
+    if (c >= it.c0) rn = __ldg(a.mflux + it.base + (long)c * sd);
+    const typename MatSel<ORD, VT>::type mat = MatSel<ORD, VT>::get(a.vtab, a.vst, voff, c + 1);
+    double st[ORD], E, O;
+#pragma unroll
+    for (int s = 0; s < ORD; s++) st[s] = rb[off[s]];
+    weno_EO<ORD>(st, mat, E, O);
+    if (c >= it.c0) {
+      double flux = rn * (rn > 0.0 ? Rp : E - O);
+      if (DIR == 2 && c == 0) flux = 0.0;                       // bottom wall: rw = 0 (Dycore.h:477,482)
+      fl[it.base + (long)c * sd] = flux;
+    }
+    Rp = E + O;
+    if (more) {
+      rb[off[0]] = nq * rcp_pos(nr);
+      const int o0 = off[0];
+#pragma unroll
+      for (int s = 0; s < ORD - 1; s++) off[s] = off[s + 1];
+      off[ORD - 1] = o0;
+    }
+  }
+  if (DIR == 2 && it.c1 == n) fl[it.base + (long)n * sd] = 0.0;   // top wall: rw = 0 (Dycore.h:496)
+}
+
+}  // namespace awfl

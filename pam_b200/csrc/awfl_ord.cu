@@ -1,6 +1,8 @@
 // One translation unit per reconstruction order (-DAWFL_ORD_INST=3|5|7|9): instantiates the order-templated kernels of
 // awfl_sweep.cuh and defines the host launchers declared in awfl_types.h.
+#include <set>
 #include "awfl_sweep.cuh"
+#include "awfl_march.cuh"
 
 #ifndef AWFL_ORD_INST
 #error "compile with -DAWFL_ORD_INST=3|5|7|9"
@@ -31,6 +33,55 @@ void OrdLaunch<ORD>::tracer_sweep(cudaStream_t s, const Geom &g, const TracerSwe
   else if (shared) k_sweep_tracer<ORD, 2, true><<<blocks, 32 * WPB, 0, s>>>(g, a);
   else k_sweep_tracer<ORD, 2, false><<<blocks, 32 * WPB, 0, s>>>(g, a);
 }
+
+// Launch a marching kernel with its dynamic shared-memory ring; the first launch of each kernel opts in to > 48 KB of
+// dynamic shared memory and asks for the largest shared-memory carve-out.
+template <class... KArgs, class... Args>
+static void launch_march(void (*kernel)(KArgs...), unsigned blocks, size_t bytes, cudaStream_t s, const Args &...args) {
+  static std::set<const void *> configured;
+  if (!configured.count((const void *)kernel)) {
+    cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+    cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+    configured.insert((const void *)kernel);
+  }
+  kernel<<<blocks, MT, bytes, s>>>(args...);
+}
+#define AWFL_LAUNCH_MARCH(KERNEL, BYTES, ...) launch_march(KERNEL, blocks, BYTES, s, __VA_ARGS__)
+
+template <int ORD>
+void OrdLaunch<ORD>::march_state(cudaStream_t s, const Geom &g, const Phys &ph, const SweepArgs &a, int dir, int mode, int vt, long items) {
+  const unsigned blocks = (unsigned)((items + WPB - 1) / WPB);
+  constexpr size_t B = MarchCfg<ORD>::SMEM_STATE;
+  // x and y sweeps only ever accumulate (MODE 0); the z sweep is always the last of a stage (MODE 1 or 2)
+  if (dir == 0) AWFL_LAUNCH_MARCH((k_march_state<ORD, 0, 0, 0>), B, g, ph, a);
+  else if (dir == 1) AWFL_LAUNCH_MARCH((k_march_state<ORD, 1, 0, 0>), B, g, ph, a);
+  else if (mode == 1) {
+    if (vt == 1) AWFL_LAUNCH_MARCH((k_march_state<ORD, 2, 1, 1>), B, g, ph, a);
+    else AWFL_LAUNCH_MARCH((k_march_state<ORD, 2, 1, 2>), B, g, ph, a);
+  } else {
+    if (vt == 1) AWFL_LAUNCH_MARCH((k_march_state<ORD, 2, 2, 1>), B, g, ph, a);
+    else AWFL_LAUNCH_MARCH((k_march_state<ORD, 2, 2, 2>), B, g, ph, a);
+  }
+}
+
+template <int ORD>
+void OrdLaunch<ORD>::march_tracer(cudaStream_t s, const Geom &g, const TracerSweepArgs &a, int dir, int vt, long items) {
+  const unsigned blocks = (unsigned)((items + WPB - 1) / WPB);
+  constexpr size_t B = MarchCfg<ORD>::SMEM_TRACER;
+  if (dir == 0) AWFL_LAUNCH_MARCH((k_march_tracer<ORD, 0, 0>), B, g, a);
+  else if (dir == 1) AWFL_LAUNCH_MARCH((k_march_tracer<ORD, 1, 0>), B, g, a);
+  else if (vt == 1) AWFL_LAUNCH_MARCH((k_march_tracer<ORD, 2, 1>), B, g, a);
+  else AWFL_LAUNCH_MARCH((k_march_tracer<ORD, 2, 2>), B, g, a);
+}
+
+template <int ORD>
+int OrdLaunch<ORD>::upload_cvtab(cudaStream_t s, const double *host, size_t ndoubles) {
+  if (ndoubles > (size_t)AWFL_CVTAB_DOUBLES) return (int)cudaErrorInvalidValue;
+  return (int)cudaMemcpyToSymbolAsync(c_vtab, host, ndoubles * sizeof(double), 0, cudaMemcpyHostToDevice, s);
+}
+
+template <int ORD>
+size_t OrdLaunch<ORD>::cvtab_capacity() { return (size_t)AWFL_CVTAB_DOUBLES; }
 
 template <int ORD>
 void OrdLaunch<ORD>::hydro_pint(cudaStream_t s, const Geom &g, const Phys &ph, const HydroArgs &a, bool shared) {

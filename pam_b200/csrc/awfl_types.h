@@ -6,6 +6,7 @@ namespace awfl {
 
 enum { idR = 0, idU = 1, idV = 2, idW = 3, idT = 4, NS = 5 };
 static constexpr int WPB = 4;  // warps (work items) per block of the sweep kernels; lane = ensemble member
+static constexpr int MT = 32 * WPB;   // threads per block of the marching kernels
 
 struct Geom {
   int nz, ny, nx, nens, nt;
@@ -26,7 +27,9 @@ struct SweepArgs {
   double *mflux;          // interface mass flux of this direction
   const double *dz;       // (nz,nens)
   const double *grav_var; // (nz,nens)
-  const double *vtab;     // vertical matrices
+  const double *vtab;     // vertical matrices (global-memory copy)
+  const double *rdz;      // 1/dz (nz,nens)
+  long vst;               // element stride of vtab: nens (member-dependent grid) or 1 (shared grid)
   double a, b, c;         // SSPRK3 stage coefficients (c = b*dt)
   int first;              // 1: this is the first sweep of the stage (tend is written, not accumulated)
   int nseg;
@@ -38,6 +41,7 @@ struct TracerSweepArgs {
   const double *mflux;  // interface mass flux of this direction
   double *tflux;        // nt fields of interface fluxes for this direction
   const double *vtab;
+  long vst;             // element stride of vtab: nens or 1
   int nseg;
   long items_per_tracer;
 };
@@ -55,6 +59,11 @@ struct HydroArgs {
 template <int ORD> struct OrdLaunch {
   static void state_sweep(cudaStream_t s, const Geom &g, const Phys &ph, const SweepArgs &a, int dir, int mode, bool shared, long items);
   static void tracer_sweep(cudaStream_t s, const Geom &g, const TracerSweepArgs &a, int dir, bool shared, long items);
+  // cell-centred marching kernels (awfl_march.cuh); vt: 0 constant horizontal, 1 constant-bank vertical, 2 global vertical
+  static void march_state(cudaStream_t s, const Geom &g, const Phys &ph, const SweepArgs &a, int dir, int mode, int vt, long items);
+  static void march_tracer(cudaStream_t s, const Geom &g, const TracerSweepArgs &a, int dir, int vt, long items);
+  static int upload_cvtab(cudaStream_t s, const double *host, size_t ndoubles);   // returns a cudaError_t
+  static size_t cvtab_capacity();
   static void hydro_pint(cudaStream_t s, const Geom &g, const Phys &ph, const HydroArgs &a, bool shared);
   static void reconstruct(cudaStream_t s, const double *st, int n, int ind, int level, int iens, int nens, const double *vtab, bool shared, double *out);
 };

@@ -59,15 +59,14 @@ AWFL_DEFINE_CST(5)
 AWFL_DEFINE_CST(7)
 AWFL_DEFINE_CST(9)
 
-// 1/x for x > 0, normal range: MUFU.RCP64H seed (~2^-20) + two Newton-Raphson steps, <= ~1 ulp.
+// 1/x for x > 0, normal range: MUFU.RCP64H seed (relative error e0 ~ 2^-20) + one cubically convergent step
+// r*(1 + e + e^2), e = 1 - x*r  (error e0^3 ~ 2^-60, then rounding): <= ~1 ulp in 3 DFMA, no slow path.
 __device__ __forceinline__ double rcp_pos(double x) {
   double r;
   asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
-  double e = fma(-x, r, 1.0);
-  r = fma(r, e, r);
-  e = fma(-x, r, 1.0);
-  r = fma(r, e, r);
-  return r;
+  const double e = fma(-x, r, 1.0);
+  const double t = fma(e, e, e);
+  return fma(r, t, r);
 }
 
 // Horizontal (uniform dx) matrices: compile-time constants folded into FMA immediates / constant bank.
@@ -87,6 +86,22 @@ template <int ORD> struct VMat {
   long st;
   __device__ __forceinline__ double lo(int i, int s, int ii) const { return __ldg(p + ((i * HS + s) * HS + ii) * st); }
   __device__ __forceinline__ double br(int s, int ii) const { return __ldg(p + (HS * HS * HS + s * ORD + ii) * st); }
+};
+
+// Vertical matrices of a grid shared by all ensemble members, held in the constant bank: the level index is uniform
+// across a warp of the marching kernels, so every element is one constant-cache load (no vector-memory traffic).
+// Same per-level layout as VMat. Uploaded by OrdLaunch<ORD>::upload_cvtab.
+#ifndef AWFL_CVTAB_DOUBLES
+#define AWFL_CVTAB_DOUBLES 7680
+#endif
+static __constant__ double c_vtab[AWFL_CVTAB_DOUBLES];
+template <int ORD> struct CMat {
+  static constexpr bool is_const = false;
+  static constexpr int HS = (ORD + 1) / 2;
+  static constexpr int NEL = HS * HS * HS + ORD * ORD;
+  int base;
+  __device__ __forceinline__ double lo(int i, int s, int ii) const { return c_vtab[base + (i * HS + s) * HS + ii]; }
+  __device__ __forceinline__ double br(int s, int ii) const { return c_vtab[base + HS * HS * HS + s * ORD + ii]; }
 };
 
 // WENO-limited polynomial of the centre cell of stencil u[0..ORD-1], returned as its even (E) and odd (O) parts at

@@ -4,7 +4,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libawfl_b200.so")
+LIB_PATH = os.environ.get("AWFL_B200_LIB") or os.path.join(_HERE, "libawfl_b200.so")   # env override: kernel experiments
 
 c_double_p = C.POINTER(C.c_double)
 

@@ -318,7 +318,6 @@ struct awfl_handle {
   double *dz, *rdz, *grav_var, *vtab, *vs2c, *vwrl, *pint;
   std::vector<double> vtab_h;   // host copy of the kernel table (constant-bank upload)
   bool use_cvtab;               // shared vertical grid whose table fits the constant bank
-  bool sweep_v1;                // AWFL_SWEEP=v1: the register-window sweep kernels (kept for A/B measurements)
   double *dt_min_d, *dt_min_h;   // device scalar + pinned host scalar
   double *mass_d;
   unsigned char *positive_d, *adds_mass_d;
@@ -483,7 +482,7 @@ static long items_for(const awfl_handle *h, int dir, int nseg) {
 // order may have replaced it; its kernels may still be running on another stream, so a change of owner synchronises
 // the device first (never happens with one handle per device and order, the normal case).
 static int ensure_cvtab(awfl_handle *h) {
-  if (!h->use_cvtab || h->sweep_v1) return 0;
+  if (!h->use_cvtab) return 0;
   const int slot = ord_slot(h->ord);
   if (g_cvtab_owner[slot] == h) return 0;
   if (g_cvtab_owner[slot] != nullptr) CK(cudaDeviceSynchronize());
@@ -502,8 +501,7 @@ static int ensure_cvtab(awfl_handle *h) {
 static void launch_state_sweep(awfl_handle *h, int dir, int mode, const SweepArgs &a) {
   const long items = items_for(h, dir, a.nseg);
   ProfScope ps(h, KC_STATE_X + dir);
-  if (h->sweep_v1) { AWFL_ORD_DISPATCH(state_sweep(h->stream, h->g, h->ph, a, dir, mode, h->shared_grid, items)); }
-  else { AWFL_ORD_DISPATCH(march_state(h->stream, h->g, h->ph, a, dir, mode, dir == 2 ? (h->use_cvtab ? 1 : 2) : 0, items)); }
+  AWFL_ORD_DISPATCH(march_state(h->stream, h->g, h->ph, a, dir, mode, dir == 2 ? (h->use_cvtab ? 1 : 2) : 0, items));
 }
 
 static void launch_tracer_sweep(awfl_handle *h, int dir, TracerSweepArgs a) {
@@ -511,8 +509,7 @@ static void launch_tracer_sweep(awfl_handle *h, int dir, TracerSweepArgs a) {
   a.items_per_tracer = items_for(h, dir, a.nseg);
   const long items = a.items_per_tracer * h->g.nt;
   ProfScope ps(h, KC_TRACER_X + dir);
-  if (h->sweep_v1) { AWFL_ORD_DISPATCH(tracer_sweep(h->stream, h->g, a, dir, h->shared_grid, items)); }
-  else { AWFL_ORD_DISPATCH(march_tracer(h->stream, h->g, a, dir, dir == 2 ? (h->use_cvtab ? 1 : 2) : 0, items)); }
+  AWFL_ORD_DISPATCH(march_tracer(h->stream, h->g, a, dir, dir == 2 ? (h->use_cvtab ? 1 : 2) : 0, items));
 }
 
 // One semi-discrete right-hand side + stage combination.
@@ -592,7 +589,7 @@ int awfl_create(const awfl_config *cfg, awfl_handle **out) {
   const double C0 = cfg->C0 != 0.0 ? cfg->C0 : pow(R_d * pow(cfg->p0, -kappa), gamma);
   h->kappa = kappa;
   h->ph.R_d = R_d; h->ph.R_v = cfg->R_v; h->ph.C0 = C0; h->ph.gamma = gamma; h->ph.grav = cfg->grav;
-  h->seg_len = 16;
+  h->seg_len = 32;
   if (const char *s = getenv("AWFL_SEG_LEN")) { int v = atoi(s); if (v >= 4) h->seg_len = v; }
   auto bail = [&](const std::string &m) { g_create_err = m; awfl_destroy(h); return 1; };
   cudaError_t ce = cudaSetDevice(cfg->device);
@@ -612,8 +609,6 @@ int awfl_create(const awfl_config *cfg, awfl_handle **out) {
   if (getenv("AWFL_FORCE_PER_ENS_GRID")) h->shared_grid = false;
   std::vector<double> vs2c, vwrl, vtab;
   build_vertical(h->ord, g.nz, g.nens, cfg->dz_host, h->shared_grid, vs2c, vwrl, vtab);
-  h->sweep_v1 = false;
-  if (const char *s = getenv("AWFL_SWEEP")) h->sweep_v1 = std::string(s) == "v1";
   h->use_cvtab = h->shared_grid && vtab.size() <= OrdLaunch<5>::cvtab_capacity() && !getenv("AWFL_NO_CVTAB");
   if (h->use_cvtab) h->vtab_h = vtab;
   const size_t fb = sizeof(double) * (size_t)g.ncell;

@@ -21,9 +21,24 @@ namespace awfl {
 // Ring fields in marching order: the acoustic pair first, then the four advected quantities, then density.
 enum { RF_M = 0, RF_P, RF_U, RF_V, RF_W, RF_T, RF_R, RF_COUNT };
 
+#ifndef AWFL_MINB5
+#define AWFL_MINB5 12
+#endif
+#ifndef AWFL_MINB5_Z
+#define AWFL_MINB5_Z 16
+#endif
+#ifndef AWFL_MINB5_TR
+#define AWFL_MINB5_TR 16
+#endif
+#ifndef AWFL_NV
+#define AWFL_NV 2      // reconstructions evaluated together in the state march (1 or 2)
+#endif
+
 template <int ORD> struct MarchCfg {
-  static constexpr int MINB = ORD == 3 ? 6 : (ORD == 5 ? 4 : (ORD == 7 ? 3 : 2));       // resident blocks per SM (state)
-  static constexpr int MINB_TR = ORD == 3 ? 8 : (ORD == 5 ? 6 : (ORD == 7 ? 4 : 3));    // resident blocks per SM (tracer)
+  // resident one-warp blocks per SM
+  static constexpr int MINB = ORD == 3 ? 20 : (ORD == 5 ? AWFL_MINB5 : (ORD == 7 ? 10 : 8));      // horizontal marches
+  static constexpr int MINB_Z = ORD == 3 ? 20 : (ORD == 5 ? AWFL_MINB5_Z : (ORD == 7 ? 10 : 8));  // vertical march (measured: ord 5 prefers 16 x 128 registers)
+  static constexpr int MINB_TR = ORD == 3 ? 24 : (ORD == 5 ? AWFL_MINB5_TR : (ORD == 7 ? 12 : 8));
   // per thread: the window ring (RF_COUNT fields x ORD cells) + the previous interface's 5 fluxes + 4 right-edge values
   static constexpr int COLS_STATE = RF_COUNT * ORD + NS + 4;
   static constexpr size_t SMEM_STATE = (size_t)COLS_STATE * MT * sizeof(double);
@@ -35,6 +50,28 @@ template <int ORD> struct MarchCfg {
 __device__ __forceinline__ double pow_pos(double x, double g) { return exp(g * log(x)); }
 
 struct Raw { double r, ru, rv, rw, rt; };
+
+// NV reconstructions on consecutive ring columns. A real function call on purpose: inlined into the march loops, ptxas
+// hoists the ~80 loop-invariant constant-bank loads of the WENO tables out of the loop, runs out of uniform registers and
+// spills them (measured: 500 B of spills in the tracer march). Behind a call boundary the tables are read where they
+// are used.
+template <int NV> struct EOn { double E[NV], O[NV]; };
+template <int ORD> __device__ __forceinline__ int ring_slot(int head, int s) {
+  const int t = head + s;
+  return (t >= ORD ? t - ORD : t) * MT;
+}
+template <int ORD, int NV, class M>
+__device__ __noinline__ EOn<NV> weno_ring(const double *fb, int head, M m) {
+  double u[NV][ORD];
+#pragma unroll
+  for (int v = 0; v < NV; v++) {
+#pragma unroll
+    for (int s = 0; s < ORD; s++) u[v][s] = fb[(v * ORD) * MT + ring_slot<ORD>(head, s)];
+  }
+  EOn<NV> r;
+  weno_EO_n<ORD, NV>(u, m, r.E, r.O);
+  return r;
+}
 
 // Matrix provider of a step: VT 0 = constant horizontal tables, 1 = vertical tables in the constant bank (all members
 // share one vertical grid), 2 = vertical tables in global memory (member-dependent grid, or table too large).
@@ -63,7 +100,7 @@ template <int ORD> struct MatSel<ORD, 2> {
 //   MODE 2: last sweep: finish the tendency and write it to qout (tendency-level parity entry point)
 // ---------------------------------------------------------------------------------------------------------------
 template <int ORD, int DIR, int MODE, int VT>
-__global__ void __launch_bounds__(MT, MarchCfg<ORD>::MINB)
+__global__ void __launch_bounds__(MT, DIR == 2 ? MarchCfg<ORD>::MINB_Z : MarchCfg<ORD>::MINB)
 k_march_state(const Geom g, const Phys ph, const SweepArgs a) {
   constexpr int HS = (ORD + 1) / 2;
   constexpr double cs = 350.0;             // Dycore.h:335
@@ -71,7 +108,9 @@ k_march_state(const Geom g, const Phys ph, const SweepArgs a) {
   constexpr int NORMAL = DIR == 0 ? idU : (DIR == 1 ? idV : idW);
   extern __shared__ double ring_smem[];
   Item it;
-  if (!decode_item<DIR>((long)blockIdx.x * WPB + (threadIdx.x >> 5), g, a.nseg, it)) return;
+  // one warp per block: the march position depends on blockIdx only, so the compiler keeps the loop control and the
+  // per-level matrix addresses in uniform registers
+  if (!decode_item<DIR>((long)blockIdx.x, g, a.nseg, it)) return;
   const int n = DIR == 0 ? g.nx : (DIR == 1 ? g.ny : g.nz);
   const long sd = stride_of(DIR, g);
   const long nc = g.ncell;
@@ -119,11 +158,9 @@ k_march_state(const Geom g, const Phys ph, const SweepArgs a) {
     rb[(RF_R * ORD) * MT + so] = r;
   };
 
-  int off[ORD];                       // ring offsets of the ORD most recent cells, oldest first
-#pragma unroll
-  for (int s = 0; s < ORD; s++) off[s] = s * MT;
+  int head = 0;                       // ring slot of the oldest of the ORD most recent cells
   const double rdd_h = DIR == 0 ? 1.0 / g.dx : 1.0 / g.dy;
-  double mL = 0.0, pL = 0.0;
+  double mL = 0.0, pL = 0.0, mRs = 0.0, mLns = 0.0;
   const int jfirst = it.c0 - 1 - (HS - 1), jlast = it.c1 + HS - 1;
   Raw cur = fetch(jfirst);
 
@@ -131,13 +168,8 @@ k_march_state(const Geom g, const Phys ph, const SweepArgs a) {
   for (int j = jfirst; j <= jlast; j++) {
     Raw nxt = cur;
     if (j < jlast) nxt = fetch(j + 1);
-    {                                  // newest cell replaces the oldest
-      const int o0 = off[0];
-      put(cur, j, o0);
-#pragma unroll
-      for (int s = 0; s < ORD - 1; s++) off[s] = off[s + 1];
-      off[ORD - 1] = o0;
-    }
+    put(cur, j, head * MT);            // newest cell replaces the oldest
+    head = head + 1 == ORD ? 0 : head + 1;
     cur = nxt;
     const int c = j - (HS - 1);        // cell whose window c-HS+1..c+HS-1 is now complete
     if (c < it.c0 - 1) continue;
@@ -149,62 +181,74 @@ k_march_state(const Geom g, const Phys ph, const SweepArgs a) {
     const long idx = it.base + (long)cc * sd;
     const int k = DIR == 2 ? cc : it.la;
     double rdd = rdd_h, rho = 0.0, gv = 0.0;
-    const int so = off[HS - 2];                // ring slot of cell c-1
+    const int so = ring_slot<ORD>(head, HS - 2);   // ring slot of cell c-1
     if (upd_on) {
       if (DIR == 2) rdd = __ldg(a.rdz + (long)k * g.nens + it.e);
       if (MODE != 0) { rho = rb[(RF_R * ORD) * MT + so]; gv = __ldg(a.grav_var + (long)k * g.nens + it.e); }
     }
-    double mR = 0.0, mLn = 0.0, rn = 0.0, pp = 0.0;
+    double rn = 0.0, pp = 0.0;
     bool up = false;
-    // one pass per reconstructed quantity: rho*u_n, p (acoustic pair), then u, v, w, theta
+    // reconstructed quantities in ring order: rho*u_n, p (acoustic pair), then u, v, w, theta -- AWFL_NV at a time
 #pragma unroll 1
-    for (int v = 0; v < 6; v++) {
-      const double *fb = rb + (v * ORD) * MT;
-      double st[ORD], E, O;
+    for (int v0 = 0; v0 < 6; v0 += AWFL_NV) {
+      // issue the read-modify-write operands of this group before the reconstruction so their latency hides behind it
+      double tl[AWFL_NV], qb[AWFL_NV];
 #pragma unroll
-      for (int s = 0; s < ORD; s++) st[s] = fb[off[s]];
-      weno_EO<ORD>(st, mat, E, O);
-      if (v == 0) { mR = E - O; mLn = E + O; continue; }
-      int l;
-      double F;
-      if (v == 1) {
-        // interface c: characteristic upwinding, Dycore.h:361-365
-        const double pR = E - O;
-        if (wall) { mL = 0.0; mR = 0.0; }
-        const double w1 = 0.5 * (pR - cs * mR);
-        const double w2 = 0.5 * (pL + cs * mL);
-        pp = w1 + w2;
-        rn = wall ? 0.0 : (w2 - w1) * rcs;
-        up = rn > 0.0;                 // Dycore.h:368: the upwind cell is c-1 when the mass flux is positive
-        mL = mLn; pL = E + O;
-        // interface mass flux for the tracer march (x,y: n entries, seam stored at 0; z: n+1 entries)
-        if (flux_on && (c < it.c1 || (DIR == 2 && c == n))) a.mflux[it.base + (long)c * sd] = rn;
-        l = idR; F = rn;
-      } else {
-        l = v - 1;                     // idU..idT
-        F = rn * (up ? fpv[(NS + v - 2) * MT] : E - O);
-        fpv[(NS + v - 2) * MT] = E + O;
-        if (l == NORMAL) F += pp;
-      }
-      if (!flux_on) continue;
-      if (upd_on) {
-        const double div = (F - fpv[l * MT]) * rdd;
-        double T = a.first ? -div : a.tend[l * nc + idx] - div;
-        if (MODE == 0) a.tend[l * nc + idx] = T;
-        else {
-          if (l == idW) T = fma(-gv, rho, T);                 // Dycore.h:560
-          if (l == idV && g.sim2d) T = 0.0;                   // Dycore.h:565
-          if (MODE == 2) a.qout[l * nc + idx] = T;
-          else {
-            // round-tripped stage input (x/rho)*rho, Dycore.h:316-319 + :527-530
-            const double rt = l == idR ? rho : rb[((RF_U + l - 1) * ORD) * MT + so] * rho;
-            double o = a.b * rt;
-            if (a.a != 0.0) o = fma(a.a, a.qbase[l * nc + idx], o);   // plain load: qout may alias qbase
-            a.qout[l * nc + idx] = fma(a.c, T, o);
-          }
+      for (int i = 0; i < AWFL_NV; i++) {
+        const int v = v0 + i, lq = v == 0 ? 0 : v - 1;
+        tl[i] = 0.0; qb[i] = 0.0;
+        if (upd_on && v > 0) {
+          if (!a.first) tl[i] = a.tend[lq * nc + idx];
+          if (MODE == 1 && a.a != 0.0) qb[i] = a.qbase[lq * nc + idx];       // plain load: qout may alias qbase
         }
       }
-      fpv[l * MT] = F;
+      const EOn<AWFL_NV> eo = weno_ring<ORD, AWFL_NV>(rb + (v0 * ORD) * MT, head, mat);
+#pragma unroll
+      for (int i = 0; i < AWFL_NV; i++) {
+        const int v = v0 + i;
+        const double E = eo.E[i], O = eo.O[i];
+        if (v == 0) { mRs = E - O; mLns = E + O; continue; }
+        int l;
+        double F;
+        if (v == 1) {
+          // interface c: characteristic upwinding, Dycore.h:361-365
+          const double pR = E - O;
+          double mR = mRs;
+          if (wall) { mL = 0.0; mR = 0.0; }
+          const double w1 = 0.5 * (pR - cs * mR);
+          const double w2 = 0.5 * (pL + cs * mL);
+          pp = w1 + w2;
+          rn = wall ? 0.0 : (w2 - w1) * rcs;
+          up = rn > 0.0;               // Dycore.h:368: the upwind cell is c-1 when the mass flux is positive
+          mL = mLns; pL = E + O;
+          // interface mass flux for the tracer march (x,y: n entries, seam stored at 0; z: n+1 entries)
+          if (flux_on && (c < it.c1 || (DIR == 2 && c == n))) a.mflux[it.base + (long)c * sd] = rn;
+          l = idR; F = rn;
+        } else {
+          l = v - 1;                   // idU..idT
+          F = rn * (up ? fpv[(NS + v - 2) * MT] : E - O);
+          fpv[(NS + v - 2) * MT] = E + O;
+          if (l == NORMAL) F += pp;
+        }
+        if (!flux_on) continue;
+        if (upd_on) {
+          const double div = (F - fpv[l * MT]) * rdd;
+          double T = tl[i] - div;
+          if (MODE == 0) a.tend[l * nc + idx] = T;
+          else {
+            if (l == idW) T = fma(-gv, rho, T);                 // Dycore.h:560
+            if (l == idV && g.sim2d) T = 0.0;                   // Dycore.h:565
+            if (MODE == 2) a.qout[l * nc + idx] = T;
+            else {
+              // round-tripped stage input (x/rho)*rho, Dycore.h:316-319 + :527-530
+              const double rt = l == idR ? rho : rb[((RF_U + l - 1) * ORD) * MT + so] * rho;
+              const double o = fma(a.a, qb[i], a.b * rt);
+              a.qout[l * nc + idx] = fma(a.c, T, o);
+            }
+          }
+        }
+        fpv[l * MT] = F;
+      }
     }
   }
 }
@@ -218,7 +262,7 @@ __global__ void __launch_bounds__(MT, MarchCfg<ORD>::MINB_TR)
 k_march_tracer(const Geom g, const TracerSweepArgs a) {
   constexpr int HS = (ORD + 1) / 2;
   extern __shared__ double ring_smem[];
-  const long gitem = (long)blockIdx.x * WPB + (threadIdx.x >> 5);
+  const long gitem = (long)blockIdx.x;                        // one warp per block (see k_march_state)
   const int tr = (int)(gitem / a.items_per_tracer);
   if (tr >= g.nt) return;
   Item it;
@@ -237,29 +281,26 @@ k_march_tracer(const Geom g, const TracerSweepArgs a) {
     else cw = c < 0 ? c + n : (c >= n ? c - n : c);            // periodic, Dycore.h:629-657
     return it.base + (long)cw * sd;
   };
-  int off[ORD];
-#pragma unroll
-  for (int s = 0; s < ORD; s++) off[s] = s * MT;
+  int head = 0;
   {
     const int cs0 = it.c0 - 1 - (HS - 1);
 #pragma unroll
     for (int s = 0; s < ORD; s++) {
       const long idx = cell_index(cs0 + s);
-      rb[off[s]] = __ldg(tq + idx) * rcp_pos(__ldg(rho + idx));        // Dycore.h:320
+      rb[s * MT] = __ldg(tq + idx) * rcp_pos(__ldg(rho + idx));        // Dycore.h:320
     }
   }
-  double Rp = 0.0;
+  double Rp = 0.0, rn_next = 0.0;
 #pragma unroll 1
   for (int c = it.c0 - 1; c < it.c1; c++) {
     const bool more = c + 1 < it.c1;
-    double nq = 0.0, nr = 1.0, rn = 0.0;
+    double nq = 0.0, nr = 1.0;
     if (more) { const long idx = cell_index(c + HS); nq = __ldg(tq + idx); nr = __ldg(rho + idx); }
-    if (c >= it.c0) rn = __ldg(a.mflux + it.base + (long)c * sd);
+    const double rn = rn_next;                                   // mass flux of interface c, loaded one step ahead
+    if (more) rn_next = __ldg(a.mflux + it.base + (long)(c + 1) * sd);
     const typename MatSel<ORD, VT>::type mat = MatSel<ORD, VT>::get(a.vtab, a.vst, voff, c + 1);
-    double st[ORD], E, O;
-#pragma unroll
-    for (int s = 0; s < ORD; s++) st[s] = rb[off[s]];
-    weno_EO<ORD>(st, mat, E, O);
+    const EOn<1> eo = weno_ring<ORD, 1>(rb, head, mat);
+    const double E = eo.E[0], O = eo.O[0];
     if (c >= it.c0) {
       double flux = rn * (rn > 0.0 ? Rp : E - O);
       if (DIR == 2 && c == 0) flux = 0.0;                       // bottom wall: rw = 0 (Dycore.h:477,482)
@@ -267,11 +308,8 @@ k_march_tracer(const Geom g, const TracerSweepArgs a) {
     }
     Rp = E + O;
     if (more) {
-      rb[off[0]] = nq * rcp_pos(nr);
-      const int o0 = off[0];
-#pragma unroll
-      for (int s = 0; s < ORD - 1; s++) off[s] = off[s + 1];
-      off[ORD - 1] = o0;
+      rb[head * MT] = nq * rcp_pos(nr);
+      head = head + 1 == ORD ? 0 : head + 1;
     }
   }
   if (DIR == 2 && it.c1 == n) fl[it.base + (long)n * sd] = 0.0;   // top wall: rw = 0 (Dycore.h:496)

@@ -10,30 +10,6 @@
 
 namespace awfl {
 
-template <int ORD>
-void OrdLaunch<ORD>::state_sweep(cudaStream_t s, const Geom &g, const Phys &ph, const SweepArgs &a, int dir, int mode, bool shared, long items) {
-  const unsigned blocks = (unsigned)((items + WPB - 1) / WPB);
-  // x and y sweeps only ever accumulate (MODE 0); the z sweep is always the last of a stage (MODE 1 or 2)
-  if (dir == 0) k_sweep_state<ORD, 0, 0, false><<<blocks, 32 * WPB, 0, s>>>(g, ph, a);
-  else if (dir == 1) k_sweep_state<ORD, 1, 0, false><<<blocks, 32 * WPB, 0, s>>>(g, ph, a);
-  else if (mode == 1) {
-    if (shared) k_sweep_state<ORD, 2, 1, true><<<blocks, 32 * WPB, 0, s>>>(g, ph, a);
-    else k_sweep_state<ORD, 2, 1, false><<<blocks, 32 * WPB, 0, s>>>(g, ph, a);
-  } else {
-    if (shared) k_sweep_state<ORD, 2, 2, true><<<blocks, 32 * WPB, 0, s>>>(g, ph, a);
-    else k_sweep_state<ORD, 2, 2, false><<<blocks, 32 * WPB, 0, s>>>(g, ph, a);
-  }
-}
-
-template <int ORD>
-void OrdLaunch<ORD>::tracer_sweep(cudaStream_t s, const Geom &g, const TracerSweepArgs &a, int dir, bool shared, long items) {
-  const unsigned blocks = (unsigned)((items + WPB - 1) / WPB);
-  if (dir == 0) k_sweep_tracer<ORD, 0, false><<<blocks, 32 * WPB, 0, s>>>(g, a);
-  else if (dir == 1) k_sweep_tracer<ORD, 1, false><<<blocks, 32 * WPB, 0, s>>>(g, a);
-  else if (shared) k_sweep_tracer<ORD, 2, true><<<blocks, 32 * WPB, 0, s>>>(g, a);
-  else k_sweep_tracer<ORD, 2, false><<<blocks, 32 * WPB, 0, s>>>(g, a);
-}
-
 // Launch a marching kernel with its dynamic shared-memory ring; the first launch of each kernel opts in to > 48 KB of
 // dynamic shared memory and asks for the largest shared-memory carve-out.
 template <class... KArgs, class... Args>
@@ -50,7 +26,7 @@ static void launch_march(void (*kernel)(KArgs...), unsigned blocks, size_t bytes
 
 template <int ORD>
 void OrdLaunch<ORD>::march_state(cudaStream_t s, const Geom &g, const Phys &ph, const SweepArgs &a, int dir, int mode, int vt, long items) {
-  const unsigned blocks = (unsigned)((items + WPB - 1) / WPB);
+  const unsigned blocks = (unsigned)items;
   constexpr size_t B = MarchCfg<ORD>::SMEM_STATE;
   // x and y sweeps only ever accumulate (MODE 0); the z sweep is always the last of a stage (MODE 1 or 2)
   if (dir == 0) AWFL_LAUNCH_MARCH((k_march_state<ORD, 0, 0, 0>), B, g, ph, a);
@@ -66,7 +42,7 @@ void OrdLaunch<ORD>::march_state(cudaStream_t s, const Geom &g, const Phys &ph, 
 
 template <int ORD>
 void OrdLaunch<ORD>::march_tracer(cudaStream_t s, const Geom &g, const TracerSweepArgs &a, int dir, int vt, long items) {
-  const unsigned blocks = (unsigned)((items + WPB - 1) / WPB);
+  const unsigned blocks = (unsigned)items;
   constexpr size_t B = MarchCfg<ORD>::SMEM_TRACER;
   if (dir == 0) AWFL_LAUNCH_MARCH((k_march_tracer<ORD, 0, 0>), B, g, a);
   else if (dir == 1) AWFL_LAUNCH_MARCH((k_march_tracer<ORD, 1, 0>), B, g, a);

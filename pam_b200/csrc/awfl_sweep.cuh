@@ -1,5 +1,6 @@
-// Order-templated device code of the AWFL time step: the marching sweep kernels, the hydrostatic interface-pressure
-// kernel and the reconstruct test hook. Included only by awfl_ord.cu (one instantiation per translation unit).
+// Order-templated device code shared by the AWFL kernels: primitive recovery and wall ghost cells, the work-item decode
+// of the marching kernels (awfl_march.cuh), the hydrostatic interface-pressure kernel and the reconstruct test hook.
+// Included only by awfl_ord.cu (one instantiation per translation unit).
 #pragma once
 #include <math.h>
 #include "awfl_types.h"
@@ -93,236 +94,6 @@ __device__ __forceinline__ bool decode_item(long item, const Geom &g, int nseg, 
     it.base = ((long)it.la * g.nx + it.lb) * g.nens + it.e;
   }
   return true;
-}
-
-// ---------------------------------------------------------------------------------------------------------------
-// State sweep: Dycore.h:334-519 (flux kernel, one direction) + :553-566 (flux divergence, gravity) and, on the last
-// sweep of a stage, the SSPRK3 stage combination Dycore.h:162-165 / :182-187 / :206-211.
-//   MODE 0: write (first sweep) or accumulate this direction's flux divergence into tend[5]
-//   MODE 1: last sweep: finish the tendency and write qout = a*qbase + b*roundtrip(qin) + c*tend
-//   MODE 2: last sweep: finish the tendency and write it to tend_out (tendency-level parity entry point)
-// ---------------------------------------------------------------------------------------------------------------
-
-
-template <int ORD, int DIR, int MODE, bool SHARED>
-__global__ void __launch_bounds__(32 * WPB)
-k_sweep_state(const Geom g, const Phys ph, const SweepArgs a) {
-  constexpr int HS = (ORD + 1) / 2;
-  constexpr double cs = 350.0;   // Dycore.h:335
-  Item it;
-  if (!decode_item<DIR>((long)blockIdx.x * WPB + (threadIdx.x >> 5), g, a.nseg, it)) return;
-  const int n = DIR == 0 ? g.nx : (DIR == 1 ? g.ny : g.nz);
-  const long sd = stride_of(DIR, g);
-  const long nc = g.ncell;
-  const double *__restrict__ q = a.qin;
-
-  // wall contexts (z only)
-  WallCtx wb, wt;
-  if (DIR == 2) {
-    if (it.c0 - HS < 0) {
-      double r0; Prim b = load_prim<DIR>(q, it.base, nc, ph, r0);
-      wb = make_wall(b, r0, __ldg(a.dz + it.e), ph);
-    }
-    if (it.c1 + HS - 1 >= n) {
-      double r0; Prim b = load_prim<DIR>(q, it.base + (long)(n - 1) * sd, nc, ph, r0);
-      wt = make_wall(b, r0, __ldg(a.dz + (long)(n - 1) * g.nens + it.e), ph);
-    }
-  }
-  auto get_cell = [&](int c) -> Prim {
-    double rr;
-    if (DIR == 2) {
-      if (c < 0) return ghost_prim(wb, -c, 1.0, ph);
-      if (c >= n) return ghost_prim(wt, c - n + 1, -1.0, ph);
-      return load_prim<DIR>(q, it.base + (long)c * sd, nc, ph, rr);
-    } else {
-      int cw = c < 0 ? c + n : (c >= n ? c - n : c);
-      return load_prim<DIR>(q, it.base + (long)cw * sd, nc, ph, rr);
-    }
-  };
-
-  // window of ORD+1 cells: W[s] = cell f-HS+s for the current interface f
-  double Wu[ORD + 1], Wv[ORD + 1], Ww[ORD + 1], Wt[ORD + 1], Wm[ORD + 1], Wp[ORD + 1];
-#pragma unroll
-  for (int s = 0; s < ORD + 1; s++) {
-    Prim c = get_cell(it.c0 - HS + s);
-    Wu[s] = c.u; Wv[s] = c.v; Ww[s] = c.w; Wt[s] = c.t; Wm[s] = c.m; Wp[s] = c.p;
-  }
-  const long vst = SHARED ? 1 : g.nens;
-  auto vmat = [&](int level) -> VMat<ORD> {
-    VMat<ORD> m;
-    m.p = a.vtab + (long)level * VMat<ORD>::NEL * vst + (SHARED ? 0 : it.e);
-    m.st = vst;
-    return m;
-  };
-  HMat<ORD> hm;
-
-  // acoustic polynomial of cell c0-1 -> left states of interface c0
-  double mL, pL;
-  {
-    double sm[ORD], sp[ORD], E, O;
-#pragma unroll
-    for (int s = 0; s < ORD; s++) { sm[s] = Wm[s]; sp[s] = Wp[s]; }
-    if (DIR == 2) { VMat<ORD> vm = vmat(it.c0); weno_EO<ORD>(sm, vm, E, O); mL = E + O; weno_EO<ORD>(sp, vm, E, O); pL = E + O; }
-    else          { weno_EO<ORD>(sm, hm, E, O); mL = E + O; weno_EO<ORD>(sp, hm, E, O); pL = E + O; }
-  }
-  double Fp[NS];
-#pragma unroll
-  for (int l = 0; l < NS; l++) Fp[l] = 0.0;
-
-  for (int f = it.c0; f <= it.c1; f++) {
-    // acoustic polynomial of cell f -> right states of interface f and left states of interface f+1
-    double mR, pR, mLn, pLn;
-    {
-      double sm[ORD], sp[ORD], E, O;
-#pragma unroll
-      for (int s = 0; s < ORD; s++) { sm[s] = Wm[s + 1]; sp[s] = Wp[s + 1]; }
-      if (DIR == 2) { VMat<ORD> vm = vmat(f + 1); weno_EO<ORD>(sm, vm, E, O); mR = E - O; mLn = E + O; weno_EO<ORD>(sp, vm, E, O); pR = E - O; pLn = E + O; }
-      else          { weno_EO<ORD>(sm, hm, E, O); mR = E - O; mLn = E + O; weno_EO<ORD>(sp, hm, E, O); pR = E - O; pLn = E + O; }
-    }
-    const bool wall = (DIR == 2) && (f == 0 || f == n);   // Dycore.h:477,482,496
-    if (wall) { mL = 0.0; mR = 0.0; }
-    // characteristic upwinding, Dycore.h:361-365
-    const double w1 = 0.5 * (pR - cs * mR);
-    const double w2 = 0.5 * (pL + cs * mL);
-    const double pp = w1 + w2;
-    double rn = (w2 - w1) / cs;
-    if (wall) rn = 0.0;
-    const int upw = rn > 0.0 ? 0 : 1;   // Dycore.h:368
-    double F[NS];
-    F[idR] = rn;
-    {
-      double su[ORD], sv[ORD], sw[ORD], st[ORD], E, O;
-#pragma unroll
-      for (int s = 0; s < ORD; s++) {
-        su[s] = upw ? Wu[s + 1] : Wu[s];
-        sv[s] = upw ? Wv[s + 1] : Wv[s];
-        sw[s] = upw ? Ww[s + 1] : Ww[s];
-        st[s] = upw ? Wt[s + 1] : Wt[s];
-      }
-      const double sg = upw ? -1.0 : 1.0;
-      if (DIR == 2) {
-        VMat<ORD> vm = vmat(f + upw);
-        weno_EO<ORD>(su, vm, E, O); F[idU] = rn * fma(sg, O, E);
-        weno_EO<ORD>(sv, vm, E, O); F[idV] = rn * fma(sg, O, E);
-        weno_EO<ORD>(sw, vm, E, O); F[idW] = rn * fma(sg, O, E);
-        weno_EO<ORD>(st, vm, E, O); F[idT] = rn * fma(sg, O, E);
-      } else {
-        weno_EO<ORD>(su, hm, E, O); F[idU] = rn * fma(sg, O, E);
-        weno_EO<ORD>(sv, hm, E, O); F[idV] = rn * fma(sg, O, E);
-        weno_EO<ORD>(sw, hm, E, O); F[idW] = rn * fma(sg, O, E);
-        weno_EO<ORD>(st, hm, E, O); F[idT] = rn * fma(sg, O, E);
-      }
-    }
-    F[DIR == 0 ? idU : (DIR == 1 ? idV : idW)] += pp;
-
-    // interface mass flux for the tracer sweep (x,y: n entries, seam stored at 0; z: n+1 entries)
-    if (f < it.c1 || (DIR == 2 && f == n)) a.mflux[it.base + (long)f * sd] = rn;
-
-    if (f > it.c0) {
-      const int c = f - 1;
-      const long idx = it.base + (long)c * sd;
-      const int k = DIR == 2 ? c : it.la;
-      const double dd = DIR == 0 ? g.dx : (DIR == 1 ? g.dy : __ldg(a.dz + (long)k * g.nens + it.e));
-      double T[NS];
-#pragma unroll
-      for (int l = 0; l < NS; l++) {
-        const double div = (F[l] - Fp[l]) / dd;
-        T[l] = a.first ? -div : a.tend[l * nc + idx] - div;
-      }
-      if (MODE == 0) {
-#pragma unroll
-        for (int l = 0; l < NS; l++) a.tend[l * nc + idx] = T[l];
-      } else {
-        const double rho = __ldg(q + idx);
-        T[idW] += -__ldg(a.grav_var + (long)k * g.nens + it.e) * rho;   // Dycore.h:560
-        if (g.sim2d) T[idV] = 0.0;                                       // Dycore.h:565
-        if (MODE == 2) {
-#pragma unroll
-          for (int l = 0; l < NS; l++) a.qout[l * nc + idx] = T[l];
-        } else {
-          // round-tripped stage input (x/rho)*rho, Dycore.h:316-319 + :527-530
-          double rt[NS];
-          rt[idR] = rho; rt[idU] = Wu[HS - 1] * rho; rt[idV] = Wv[HS - 1] * rho; rt[idW] = Ww[HS - 1] * rho; rt[idT] = Wt[HS - 1] * rho;
-#pragma unroll
-          for (int l = 0; l < NS; l++) {
-            double o = fma(a.c, T[l], a.b * rt[l]);
-            if (a.a != 0.0) o = fma(a.a, a.qbase[l * nc + idx], a.b * rt[l]) + a.c * T[l];   // plain load: qout may alias qbase
-            a.qout[l * nc + idx] = o;
-          }
-        }
-      }
-    }
-#pragma unroll
-    for (int l = 0; l < NS; l++) Fp[l] = F[l];
-    mL = mLn; pL = pLn;
-    if (f < it.c1) {
-#pragma unroll
-      for (int s = 0; s < ORD; s++) { Wu[s] = Wu[s + 1]; Wv[s] = Wv[s + 1]; Ww[s] = Ww[s + 1]; Wt[s] = Wt[s + 1]; Wm[s] = Wm[s + 1]; Wp[s] = Wp[s + 1]; }
-      Prim c = get_cell(f + HS);
-      Wu[ORD] = c.u; Wv[ORD] = c.v; Ww[ORD] = c.w; Wt[ORD] = c.t; Wm[ORD] = c.m; Wp[ORD] = c.p;
-    }
-  }
-}
-
-// ---------------------------------------------------------------------------------------------------------------
-// Tracer sweep: the tracer part of Dycore.h:381-385 / :434-438 / :513-517. flux = massflux * upwind WENO edge value
-// of (tracer/rho). Work item = (tracer, line, segment, ensemble tile).
-// ---------------------------------------------------------------------------------------------------------------
-
-
-template <int ORD, int DIR, bool SHARED>
-__global__ void __launch_bounds__(32 * WPB)
-k_sweep_tracer(const Geom g, const TracerSweepArgs a) {
-  constexpr int HS = (ORD + 1) / 2;
-  const long gitem = (long)blockIdx.x * WPB + (threadIdx.x >> 5);
-  const int tr = (int)(gitem / a.items_per_tracer);
-  if (tr >= g.nt) return;
-  Item it;
-  if (!decode_item<DIR>(gitem % a.items_per_tracer, g, a.nseg, it)) return;
-  const int n = DIR == 0 ? g.nx : (DIR == 1 ? g.ny : g.nz);
-  const long sd = stride_of(DIR, g);
-  const long nc = g.ncell;
-  const double *__restrict__ rho = a.qin;
-  const double *__restrict__ tq = a.qin + (long)(NS + tr) * nc;
-  double *__restrict__ fl = a.tflux + (long)tr * (DIR == 2 ? nc + nc / g.nz : nc);
-  auto get_q = [&](int c) -> double {
-    int cw;
-    if (DIR == 2) cw = c < 0 ? 0 : (c >= n ? n - 1 : c);       // wall: zero-gradient mixing ratio, Dycore.h:674-677
-    else cw = c < 0 ? c + n : (c >= n ? c - n : c);            // periodic, Dycore.h:629-657
-    const long idx = it.base + (long)cw * sd;
-    return __ldg(tq + idx) / __ldg(rho + idx);                 // Dycore.h:320
-  };
-  double W[ORD + 1];
-#pragma unroll
-  for (int s = 0; s < ORD + 1; s++) W[s] = get_q(it.c0 - HS + s);
-  const long vst = SHARED ? 1 : g.nens;
-  HMat<ORD> hm;
-  for (int f = it.c0; f < it.c1; f++) {
-    const double rn = __ldg(a.mflux + it.base + (long)f * sd);
-    double flux = 0.0;
-    if (!(DIR == 2 && f == 0)) {
-      const int upw = rn > 0.0 ? 0 : 1;
-      double st[ORD], E, O;
-#pragma unroll
-      for (int s = 0; s < ORD; s++) st[s] = upw ? W[s + 1] : W[s];
-      if (DIR == 2) {
-        VMat<ORD> vm;
-        vm.p = a.vtab + (long)(f + upw) * VMat<ORD>::NEL * vst + (SHARED ? 0 : it.e);
-        vm.st = vst;
-        weno_EO<ORD>(st, vm, E, O);
-      } else {
-        weno_EO<ORD>(st, hm, E, O);
-      }
-      flux = rn * (upw ? E - O : E + O);
-    }
-    fl[it.base + (long)f * sd] = flux;
-    if (f + 1 < it.c1) {
-#pragma unroll
-      for (int s = 0; s < ORD; s++) W[s] = W[s + 1];
-      W[ORD] = get_q(f + HS);
-    }
-  }
-  if (DIR == 2 && it.c1 == n) fl[it.base + (long)n * sd] = 0.0;   // top wall: rw = 0 (Dycore.h:496)
 }
 
 // ---------------------------------------------------------------------------------------------------------------

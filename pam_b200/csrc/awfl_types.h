@@ -5,8 +5,7 @@
 namespace awfl {
 
 enum { idR = 0, idU = 1, idV = 2, idW = 3, idT = 4, NS = 5 };
-static constexpr int WPB = 4;  // warps (work items) per block of the sweep kernels; lane = ensemble member
-static constexpr int MT = 32 * WPB;   // threads per block of the marching kernels
+static constexpr int MT = 32;  // threads per block of the marching kernels: ONE warp (work item) per block; lane = ensemble member
 
 struct Geom {
   int nz, ny, nx, nens, nt;
@@ -18,7 +17,7 @@ struct Phys {
   double R_d, R_v, C0, gamma, grav;
 };
 
-// State sweep arguments (k_sweep_state)
+// State march arguments (k_march_state)
 struct SweepArgs {
   const double *qin;      // stage input, N fields
   const double *qbase;    // step-start state (MODE 1, a != 0)
@@ -35,7 +34,7 @@ struct SweepArgs {
   int nseg;
 };
 
-// Tracer sweep arguments (k_sweep_tracer)
+// Tracer march arguments (k_march_tracer)
 struct TracerSweepArgs {
   const double *qin;    // stage input, N fields (rho = field 0, tracers from field 5)
   const double *mflux;  // interface mass flux of this direction
@@ -57,8 +56,6 @@ struct HydroArgs {
 
 // Per-order launchers, defined in awfl_ord.cu (one translation unit per reconstruction order so they build in parallel).
 template <int ORD> struct OrdLaunch {
-  static void state_sweep(cudaStream_t s, const Geom &g, const Phys &ph, const SweepArgs &a, int dir, int mode, bool shared, long items);
-  static void tracer_sweep(cudaStream_t s, const Geom &g, const TracerSweepArgs &a, int dir, bool shared, long items);
   // cell-centred marching kernels (awfl_march.cuh); vt: 0 constant horizontal, 1 constant-bank vertical, 2 global vertical
   static void march_state(cudaStream_t s, const Geom &g, const Phys &ph, const SweepArgs &a, int dir, int mode, int vt, long items);
   static void march_tracer(cudaStream_t s, const Geom &g, const TracerSweepArgs &a, int dir, int vt, long items);

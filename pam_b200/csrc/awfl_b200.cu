@@ -459,15 +459,18 @@ ProfScope::~ProfScope() {
   h->ev_used += 2;
 }
 
-static int nseg_for(const awfl_handle *h, int n) {
-  int s = (n + h->seg_len / 2) / h->seg_len;
-  return s < 1 ? 1 : s;
+// Segments per line: a power of two (the grid encodes the segment in the low bits of blockIdx.z, see decode_item),
+// chosen so that a segment is about seg_len cells and never shorter than 4.
+static int sbits_for(const awfl_handle *h, int n) {
+  int sb = 0;
+  while (sb < 4 && (n >> (sb + 1)) >= 4 && (double)n / (1 << sb) > 1.5 * h->seg_len) sb++;
+  return sb;
 }
-static long items_for(const awfl_handle *h, int dir, int nseg) {
-  const Geom &g = h->g;
-  const long netile = (g.nens + 31) / 32;
-  const long nlines = dir == 0 ? (long)g.nz * g.ny : (dir == 1 ? (long)g.nz * g.nx : (long)g.ny * g.nx);
-  return netile * nseg * nlines;
+static int labits_for(const awfl_handle *h, int dir) {
+  const int la = dir == 2 ? h->g.ny : h->g.nz;
+  int b = 0;
+  while ((1 << b) < la) b++;
+  return b;
 }
 
 #define AWFL_ORD_DISPATCH(CALL)                  \
@@ -499,17 +502,14 @@ static int ensure_cvtab(awfl_handle *h) {
 }
 
 static void launch_state_sweep(awfl_handle *h, int dir, int mode, const SweepArgs &a) {
-  const long items = items_for(h, dir, a.nseg);
   ProfScope ps(h, KC_STATE_X + dir);
-  AWFL_ORD_DISPATCH(march_state(h->stream, h->g, h->ph, a, dir, mode, dir == 2 ? (h->use_cvtab ? 1 : 2) : 0, items));
+  AWFL_ORD_DISPATCH(march_state(h->stream, h->g, h->ph, a, dir, mode, dir == 2 ? (h->use_cvtab ? 1 : 2) : 0));
 }
 
 static void launch_tracer_sweep(awfl_handle *h, int dir, TracerSweepArgs a) {
   if (h->g.nt == 0) return;
-  a.items_per_tracer = items_for(h, dir, a.nseg);
-  const long items = a.items_per_tracer * h->g.nt;
   ProfScope ps(h, KC_TRACER_X + dir);
-  AWFL_ORD_DISPATCH(march_tracer(h->stream, h->g, a, dir, dir == 2 ? (h->use_cvtab ? 1 : 2) : 0, items));
+  AWFL_ORD_DISPATCH(march_tracer(h->stream, h->g, a, dir, dir == 2 ? (h->use_cvtab ? 1 : 2) : 0));
 }
 
 // One semi-discrete right-hand side + stage combination.
@@ -527,10 +527,10 @@ static void run_stage(awfl_handle *h, const double *qin, const double *q0, doubl
     SweepArgs s;
     s.qin = qin; s.qbase = q0; s.qout = mode == 2 ? st_out : qout; s.tend = h->tend; s.mflux = h->mflux[dir];
     s.dz = h->dz; s.grav_var = h->grav_var; s.vtab = h->vtab; s.rdz = h->rdz; s.vst = h->shared_grid ? 1 : g.nens;
-    s.a = a; s.b = b; s.c = b * dt_full; s.first = d == 0; s.nseg = nseg_for(h, nn[dir]);
+    s.a = a; s.b = b; s.c = b * dt_full; s.first = d == 0; s.sbits = sbits_for(h, nn[dir]); s.labits = labits_for(h, dir);
     launch_state_sweep(h, dir, last ? mode : 0, s);
     TracerSweepArgs t;
-    t.qin = qin; t.mflux = h->mflux[dir]; t.tflux = h->tflux[dir]; t.vtab = h->vtab; t.vst = s.vst; t.nseg = s.nseg; t.items_per_tracer = 0;
+    t.qin = qin; t.mflux = h->mflux[dir]; t.tflux = h->tflux[dir]; t.vtab = h->vtab; t.vst = s.vst; t.sbits = s.sbits; t.labits = s.labits;
     launch_tracer_sweep(h, dir, t);
   }
   if (g.nt > 0) {

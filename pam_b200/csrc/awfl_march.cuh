@@ -36,13 +36,14 @@ enum { RF_M = 0, RF_P, RF_U, RF_V, RF_W, RF_T, RF_R, RF_COUNT };
 
 template <int ORD> struct MarchCfg {
   // resident one-warp blocks per SM
-  static constexpr int MINB = ORD == 3 ? 20 : (ORD == 5 ? AWFL_MINB5 : (ORD == 7 ? 10 : 8));      // horizontal marches
-  static constexpr int MINB_Z = ORD == 3 ? 20 : (ORD == 5 ? AWFL_MINB5_Z : (ORD == 7 ? 10 : 8));  // vertical march (measured: ord 5 prefers 16 x 128 registers)
-  static constexpr int MINB_TR = ORD == 3 ? 24 : (ORD == 5 ? AWFL_MINB5_TR : (ORD == 7 ? 12 : 8));
+  static constexpr int MINB = ORD == 3 ? 16 : (ORD == 5 ? AWFL_MINB5 : 8);      // horizontal marches
+  static constexpr int MINB_Z = ORD == 3 ? 16 : (ORD == 5 ? AWFL_MINB5_Z : 8);  // vertical march (measured: ord 5 prefers 16 x 128 registers)
+  static constexpr int MINB_TR = ORD == 3 ? 20 : (ORD == 5 ? AWFL_MINB5_TR : 8);
   // per thread: the window ring (RF_COUNT fields x ORD cells) + the previous interface's 5 fluxes + 4 right-edge values
-  static constexpr int COLS_STATE = RF_COUNT * ORD + NS + 4;
+  // + a staging area for the read-modify-write operands (partial tendency, base state) of the group being reconstructed
+  static constexpr int COLS_STATE = RF_COUNT * ORD + NS + 4 + 2 * AWFL_NV;
   static constexpr size_t SMEM_STATE = (size_t)COLS_STATE * MT * sizeof(double);
-  static constexpr size_t SMEM_TRACER = (size_t)ORD * MT * sizeof(double);
+  static constexpr size_t SMEM_TRACER = (size_t)(2 * (ORD + 3)) * MT * sizeof(double);   // two lines per warp
 };
 
 // x^g for x > 0 (normal range): exp(g*log(x)). Relative error <~ 3e-15 for the arguments met here (|g log x| < 20),
@@ -50,6 +51,15 @@ template <int ORD> struct MarchCfg {
 __device__ __forceinline__ double pow_pos(double x, double g) { return exp(g * log(x)); }
 
 struct Raw { double r, ru, rv, rw, rt; };
+
+// 8-byte asynchronous global -> shared copy (LDGSTS). Unlike a load into a register it is not tracked by the register
+// scoreboard, so it stays in flight across the call to weno_ring (a CALL waits for every pending register load:
+// profiles/r01c measured 28 % of the z march's stall samples there).
+__device__ __forceinline__ void cp_async8(double *smem_dst, const double *gsrc) {
+  const unsigned sa = (unsigned)__cvta_generic_to_shared(smem_dst);
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(sa), "l"(gsrc) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_all;" ::: "memory"); }
 
 // NV reconstructions on consecutive ring columns. A real function call on purpose: inlined into the march loops, ptxas
 // hoists the ~80 loop-invariant constant-bank loads of the WENO tables out of the loop, runs out of uniform registers and
@@ -62,6 +72,22 @@ template <int ORD> __device__ __forceinline__ int ring_slot(int head, int s) {
 }
 template <int ORD, int NV, class M>
 __device__ __noinline__ EOn<NV> weno_ring(const double *fb, int head, M m) {
+  double u[NV][ORD];
+#pragma unroll
+  for (int v = 0; v < NV; v++) {
+#pragma unroll
+    for (int s = 0; s < ORD; s++) u[v][s] = fb[(v * ORD) * MT + ring_slot<ORD>(head, s)];
+  }
+  EOn<NV> r;
+  weno_EO_n<ORD, NV>(u, m, r.E, r.O);
+  return r;
+}
+
+// Inlined variant for the tracer march with per-level matrices: their addresses change every step, so nothing can be
+// hoisted, and inlined the level index stays in a uniform register (behind the call it arrives in a vector register and
+// every matrix element becomes a vector LDC: profiles/r01c, 13 % of the z tracer march's stall samples).
+template <int ORD, int NV, class M>
+__device__ __forceinline__ EOn<NV> weno_ring_inl(const double *fb, int head, M m) {
   double u[NV][ORD];
 #pragma unroll
   for (int v = 0; v < NV; v++) {
@@ -110,13 +136,14 @@ k_march_state(const Geom g, const Phys ph, const SweepArgs a) {
   Item it;
   // one warp per block: the march position depends on blockIdx only, so the compiler keeps the loop control and the
   // per-level matrix addresses in uniform registers
-  if (!decode_item<DIR>((long)blockIdx.x, g, a.nseg, it)) return;
+  if (!decode_item<DIR>(g, a.sbits, a.labits, it)) return;
   const int n = DIR == 0 ? g.nx : (DIR == 1 ? g.ny : g.nz);
   const long sd = stride_of(DIR, g);
   const long nc = g.ncell;
   const double *__restrict__ q = a.qin;
   double *const rb = ring_smem + threadIdx.x;            // this thread's column: entry e at rb[e*MT]
   double *const fpv = rb + (RF_COUNT * ORD) * MT;        // previous interface: fluxes [0..4], right-edge values [5..8]
+  double *const stg = fpv + (NS + 4) * MT;               // staged read-modify-write operands of the current group
   const long voff = a.vst > 1 ? it.e : 0;
 
   auto fetch = [&](int c) -> Raw {
@@ -168,41 +195,43 @@ k_march_state(const Geom g, const Phys ph, const SweepArgs a) {
   for (int j = jfirst; j <= jlast; j++) {
     Raw nxt = cur;
     if (j < jlast) nxt = fetch(j + 1);
-    put(cur, j, head * MT);            // newest cell replaces the oldest
-    head = head + 1 == ORD ? 0 : head + 1;
-    cur = nxt;
-    const int c = j - (HS - 1);        // cell whose window c-HS+1..c+HS-1 is now complete
-    if (c < it.c0 - 1) continue;
-    const typename MatSel<ORD, VT>::type mat = MatSel<ORD, VT>::get(a.vtab, a.vst, voff, c + 1);
-    const bool flux_on = c >= it.c0;           // interface c belongs to this segment
+    const int c = j - (HS - 1);        // cell whose window c-HS+1..c+HS-1 will be complete after this put
     const bool upd_on = c > it.c0;             // cell c-1 has both interfaces
-    const bool wall = (DIR == 2) && (c == 0 || c == n);   // Dycore.h:477,482,496
     const int cc = c - 1;
     const long idx = it.base + (long)cc * sd;
     const int k = DIR == 2 ? cc : it.la;
-    double rdd = rdd_h, rho = 0.0, gv = 0.0;
-    const int so = ring_slot<ORD>(head, HS - 2);   // ring slot of cell c-1
-    if (upd_on) {
+    double rdd = rdd_h, gv = 0.0;
+    if (upd_on) {                      // per-level scalars of the update: issued before the conversion below hides them
       if (DIR == 2) rdd = __ldg(a.rdz + (long)k * g.nens + it.e);
-      if (MODE != 0) { rho = rb[(RF_R * ORD) * MT + so]; gv = __ldg(a.grav_var + (long)k * g.nens + it.e); }
+      if (MODE != 0) gv = __ldg(a.grav_var + (long)k * g.nens + it.e);
     }
+    put(cur, j, head * MT);            // newest cell replaces the oldest
+    head = head + 1 == ORD ? 0 : head + 1;
+    cur = nxt;
+    if (c < it.c0 - 1) continue;
+    const typename MatSel<ORD, VT>::type mat = MatSel<ORD, VT>::get(a.vtab, a.vst, voff, c + 1);
+    const bool flux_on = c >= it.c0;           // interface c belongs to this segment
+    const bool wall = (DIR == 2) && (c == 0 || c == n);   // Dycore.h:477,482,496
+    const int so = ring_slot<ORD>(head, HS - 2);   // ring slot of cell c-1
+    const double rho = (upd_on && MODE != 0) ? rb[(RF_R * ORD) * MT + so] : 0.0;
     double rn = 0.0, pp = 0.0;
     bool up = false;
     // reconstructed quantities in ring order: rho*u_n, p (acoustic pair), then u, v, w, theta -- AWFL_NV at a time
 #pragma unroll 1
     for (int v0 = 0; v0 < 6; v0 += AWFL_NV) {
-      // issue the read-modify-write operands of this group before the reconstruction so their latency hides behind it
-      double tl[AWFL_NV], qb[AWFL_NV];
+      // start the asynchronous copies of this group's read-modify-write operands; they land while the group is
+      // reconstructed
+      const bool ld_t = upd_on && !a.first, ld_q = upd_on && MODE == 1 && a.a != 0.0;
 #pragma unroll
       for (int i = 0; i < AWFL_NV; i++) {
         const int v = v0 + i, lq = v == 0 ? 0 : v - 1;
-        tl[i] = 0.0; qb[i] = 0.0;
-        if (upd_on && v > 0) {
-          if (!a.first) tl[i] = a.tend[lq * nc + idx];
-          if (MODE == 1 && a.a != 0.0) qb[i] = a.qbase[lq * nc + idx];       // plain load: qout may alias qbase
+        if (v > 0) {
+          if (ld_t) cp_async8(stg + (2 * i) * MT, a.tend + lq * nc + idx);
+          if (ld_q) cp_async8(stg + (2 * i + 1) * MT, a.qbase + lq * nc + idx);   // qout may alias qbase: read before the write below
         }
       }
       const EOn<AWFL_NV> eo = weno_ring<ORD, AWFL_NV>(rb + (v0 * ORD) * MT, head, mat);
+      if (ld_t || ld_q) cp_async_wait();
 #pragma unroll
       for (int i = 0; i < AWFL_NV; i++) {
         const int v = v0 + i;
@@ -233,7 +262,7 @@ k_march_state(const Geom g, const Phys ph, const SweepArgs a) {
         if (!flux_on) continue;
         if (upd_on) {
           const double div = (F - fpv[l * MT]) * rdd;
-          double T = tl[i] - div;
+          double T = (ld_t ? stg[(2 * i) * MT] : 0.0) - div;
           if (MODE == 0) a.tend[l * nc + idx] = T;
           else {
             if (l == idW) T = fma(-gv, rho, T);                 // Dycore.h:560
@@ -242,7 +271,7 @@ k_march_state(const Geom g, const Phys ph, const SweepArgs a) {
             else {
               // round-tripped stage input (x/rho)*rho, Dycore.h:316-319 + :527-530
               const double rt = l == idR ? rho : rb[((RF_U + l - 1) * ORD) * MT + so] * rho;
-              const double o = fma(a.a, qb[i], a.b * rt);
+              const double o = fma(a.a, ld_q ? stg[(2 * i + 1) * MT] : 0.0, a.b * rt);
               a.qout[l * nc + idx] = fma(a.c, T, o);
             }
           }
@@ -261,58 +290,83 @@ template <int ORD, int DIR, int VT>
 __global__ void __launch_bounds__(MT, MarchCfg<ORD>::MINB_TR)
 k_march_tracer(const Geom g, const TracerSweepArgs a) {
   constexpr int HS = (ORD + 1) / 2;
+  constexpr int NL = 2;                                       // lines marched together by one warp
   extern __shared__ double ring_smem[];
-  const long gitem = (long)blockIdx.x;                        // one warp per block (see k_march_state)
-  const int tr = (int)(gitem / a.items_per_tracer);
+  Item it;                                                    // one warp per block (see k_march_state)
+  // the two lines of a warp are adjacent levels k, k+1 for the horizontal marches and adjacent columns i, i+1 for the
+  // vertical march (an odd count repeats the last line: the same values are written twice)
+  if (!decode_item<DIR, DIR == 2 ? 1 : NL, DIR == 2 ? NL : 1>(g, a.sbits, a.labits, it)) return;
+  const int tr = it.tr;
   if (tr >= g.nt) return;
-  Item it;
-  if (!decode_item<DIR>(gitem % a.items_per_tracer, g, a.nseg, it)) return;
   const int n = DIR == 0 ? g.nx : (DIR == 1 ? g.ny : g.nz);
   const long sd = stride_of(DIR, g);
   const long nc = g.ncell;
   const double *__restrict__ rho = a.qin;
   const double *__restrict__ tq = a.qin + (long)(NS + tr) * nc;
   double *__restrict__ fl = a.tflux + (long)tr * (DIR == 2 ? nc + nc / g.nz : nc);
-  double *const rb = ring_smem + threadIdx.x;
+  long base[NL];
+  base[0] = it.base;
+  if (DIR == 2) base[1] = it.lb + 1 < g.nx ? it.base + g.nens : it.base;
+  else base[1] = it.la + 1 < g.nz ? it.base + (long)g.ny * g.nx * g.nens : it.base;
+  double *const rb = ring_smem + threadIdx.x;                 // ring of line v at rb[(v*ORD + slot)*MT]
+  double *const stg = rb + (NL * ORD) * MT;                   // staged next cell (tracer, rho) and next mass flux, per line
   const long voff = a.vst > 1 ? it.e : 0;
-  auto cell_index = [&](int c) -> long {
+  auto cell_off = [&](int c) -> long {
     int cw;
     if (DIR == 2) cw = c < 0 ? 0 : (c >= n ? n - 1 : c);       // wall: zero-gradient mixing ratio, Dycore.h:674-677
     else cw = c < 0 ? c + n : (c >= n ? c - n : c);            // periodic, Dycore.h:629-657
-    return it.base + (long)cw * sd;
+    return (long)cw * sd;
   };
   int head = 0;
   {
     const int cs0 = it.c0 - 1 - (HS - 1);
 #pragma unroll
     for (int s = 0; s < ORD; s++) {
-      const long idx = cell_index(cs0 + s);
-      rb[s * MT] = __ldg(tq + idx) * rcp_pos(__ldg(rho + idx));        // Dycore.h:320
+      const long o = cell_off(cs0 + s);
+#pragma unroll
+      for (int v = 0; v < NL; v++) rb[(v * ORD + s) * MT] = __ldg(tq + base[v] + o) * rcp_pos(__ldg(rho + base[v] + o));   // Dycore.h:320
     }
   }
-  double Rp = 0.0, rn_next = 0.0;
+  double Rp[NL] = {0.0, 0.0}, rn[NL] = {0.0, 0.0};
 #pragma unroll 1
   for (int c = it.c0 - 1; c < it.c1; c++) {
     const bool more = c + 1 < it.c1;
-    double nq = 0.0, nr = 1.0;
-    if (more) { const long idx = cell_index(c + HS); nq = __ldg(tq + idx); nr = __ldg(rho + idx); }
-    const double rn = rn_next;                                   // mass flux of interface c, loaded one step ahead
-    if (more) rn_next = __ldg(a.mflux + it.base + (long)(c + 1) * sd);
-    const typename MatSel<ORD, VT>::type mat = MatSel<ORD, VT>::get(a.vtab, a.vst, voff, c + 1);
-    const EOn<1> eo = weno_ring<ORD, 1>(rb, head, mat);
-    const double E = eo.E[0], O = eo.O[0];
-    if (c >= it.c0) {
-      double flux = rn * (rn > 0.0 ? Rp : E - O);
-      if (DIR == 2 && c == 0) flux = 0.0;                       // bottom wall: rw = 0 (Dycore.h:477,482)
-      fl[it.base + (long)c * sd] = flux;
+    if (more) {                          // asynchronous: these stay in flight across the call (see cp_async8)
+      const long o = cell_off(c + HS), om = (long)(c + 1) * sd;
+#pragma unroll
+      for (int v = 0; v < NL; v++) {
+        cp_async8(stg + (3 * v) * MT, tq + base[v] + o);
+        cp_async8(stg + (3 * v + 1) * MT, rho + base[v] + o);
+        cp_async8(stg + (3 * v + 2) * MT, a.mflux + base[v] + om);
+      }
     }
-    Rp = E + O;
+    const typename MatSel<ORD, VT>::type mat = MatSel<ORD, VT>::get(a.vtab, a.vst, voff, c + 1);
+    EOn<NL> eo;
+    if constexpr (VT != 2) eo = weno_ring<ORD, NL>(rb, head, mat); else eo = weno_ring_inl<ORD, NL>(rb, head, mat);
+#pragma unroll
+    for (int v = 0; v < NL; v++) {
+      const double E = eo.E[v], O = eo.O[v];
+      if (c >= it.c0) {
+        double flux = rn[v] * (rn[v] > 0.0 ? Rp[v] : E - O);
+        if (DIR == 2 && c == 0) flux = 0.0;                     // bottom wall: rw = 0 (Dycore.h:477,482)
+        fl[base[v] + (long)c * sd] = flux;
+      }
+      Rp[v] = E + O;
+    }
     if (more) {
-      rb[head * MT] = nq * rcp_pos(nr);
+      cp_async_wait();
+#pragma unroll
+      for (int v = 0; v < NL; v++) {
+        rb[(v * ORD + head) * MT] = stg[(3 * v) * MT] * rcp_pos(stg[(3 * v + 1) * MT]);   // Dycore.h:320
+        rn[v] = stg[(3 * v + 2) * MT];                            // mass flux of interface c+1
+      }
       head = head + 1 == ORD ? 0 : head + 1;
     }
   }
-  if (DIR == 2 && it.c1 == n) fl[it.base + (long)n * sd] = 0.0;   // top wall: rw = 0 (Dycore.h:496)
+  if (DIR == 2 && it.c1 == n) {                                 // top wall: rw = 0 (Dycore.h:496)
+#pragma unroll
+    for (int v = 0; v < NL; v++) fl[base[v] + (long)n * sd] = 0.0;
+  }
 }
 
 }  // namespace awfl

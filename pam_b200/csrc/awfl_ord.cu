@@ -13,7 +13,7 @@ namespace awfl {
 // Launch a marching kernel with its dynamic shared-memory ring; the first launch of each kernel opts in to > 48 KB of
 // dynamic shared memory and asks for the largest shared-memory carve-out.
 template <class... KArgs, class... Args>
-static void launch_march(void (*kernel)(KArgs...), unsigned blocks, size_t bytes, cudaStream_t s, const Args &...args) {
+static void launch_march(void (*kernel)(KArgs...), dim3 blocks, size_t bytes, cudaStream_t s, const Args &...args) {
   static std::set<const void *> configured;
   if (!configured.count((const void *)kernel)) {
     cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
@@ -24,9 +24,18 @@ static void launch_march(void (*kernel)(KArgs...), unsigned blocks, size_t bytes
 }
 #define AWFL_LAUNCH_MARCH(KERNEL, BYTES, ...) launch_march(KERNEL, blocks, BYTES, s, __VA_ARGS__)
 
+// lines_per_warp > 1 (tracer march): adjacent levels for the horizontal marches (first line index, inside blockIdx.z),
+// adjacent columns for the vertical march (second line index = blockIdx.y)
+static dim3 march_grid(const Geom &g, int dir, int sbits, int labits, int ntr, int lines_per_warp) {
+  const unsigned netile = (unsigned)(g.nens + 31) / 32;
+  unsigned lb = dir == 0 ? g.ny : g.nx;
+  if (dir == 2) lb = (lb + lines_per_warp - 1) / lines_per_warp;
+  return dim3(netile, lb, (unsigned)ntr << (labits + sbits));
+}
+
 template <int ORD>
-void OrdLaunch<ORD>::march_state(cudaStream_t s, const Geom &g, const Phys &ph, const SweepArgs &a, int dir, int mode, int vt, long items) {
-  const unsigned blocks = (unsigned)items;
+void OrdLaunch<ORD>::march_state(cudaStream_t s, const Geom &g, const Phys &ph, const SweepArgs &a, int dir, int mode, int vt) {
+  const dim3 blocks = march_grid(g, dir, a.sbits, a.labits, 1, 1);
   constexpr size_t B = MarchCfg<ORD>::SMEM_STATE;
   // x and y sweeps only ever accumulate (MODE 0); the z sweep is always the last of a stage (MODE 1 or 2)
   if (dir == 0) AWFL_LAUNCH_MARCH((k_march_state<ORD, 0, 0, 0>), B, g, ph, a);
@@ -41,8 +50,8 @@ void OrdLaunch<ORD>::march_state(cudaStream_t s, const Geom &g, const Phys &ph, 
 }
 
 template <int ORD>
-void OrdLaunch<ORD>::march_tracer(cudaStream_t s, const Geom &g, const TracerSweepArgs &a, int dir, int vt, long items) {
-  const unsigned blocks = (unsigned)items;
+void OrdLaunch<ORD>::march_tracer(cudaStream_t s, const Geom &g, const TracerSweepArgs &a, int dir, int vt) {
+  const dim3 blocks = march_grid(g, dir, a.sbits, a.labits, g.nt, 2);
   constexpr size_t B = MarchCfg<ORD>::SMEM_TRACER;
   if (dir == 0) AWFL_LAUNCH_MARCH((k_march_tracer<ORD, 0, 0>), B, g, a);
   else if (dir == 1) AWFL_LAUNCH_MARCH((k_march_tracer<ORD, 1, 0>), B, g, a);

@@ -62,37 +62,37 @@ __device__ __forceinline__ long stride_of(int dir, const Geom &g) {
   return dir == 0 ? (long)g.nens : (dir == 1 ? (long)g.nx * g.nens : (long)g.ny * g.nx * g.nens);
 }
 
-// Work-item decode shared by the sweep kernels: item -> (ensemble tile, segment, line); returns false if out of range.
+// Work-item decode of the marching kernels. A work item (one warp = one block) is (member tile, line, segment[, tracer]);
+// the grid carries it without any runtime division -- blockIdx.x = member tile, blockIdx.y = second line index,
+// blockIdx.z = (tracer << (labits+sbits)) | (first line index << sbits) | segment, with 2^sbits segments per line --
+// because an integer division by a runtime value goes through the floating-point reciprocal and ptxas then no longer
+// treats the march position as warp-uniform (every per-level matrix element becomes a vector load).
 struct Item {
   int e;          // ensemble member of this lane
   long base;      // linear index of cell 0 of the line (this lane)
   int c0, c1;     // cell range [c0,c1) along the sweep direction
   int la, lb;     // the two indices of the line: x: (k,j)  y: (k,i)  z: (j,i)
+  int tr;         // tracer index (tracer march)
 };
-template <int DIR>
-__device__ __forceinline__ bool decode_item(long item, const Geom &g, int nseg, Item &it) {
-  const int netile = (g.nens + 31) >> 5;
+// LA_LINES / LB_LINES: lines per work item along the first / second line index (the tracer march takes two adjacent
+// lines per warp); it.la / it.lb are then the indices of the item's FIRST line.
+template <int DIR, int LA_LINES = 1, int LB_LINES = 1>
+__device__ __forceinline__ bool decode_item(const Geom &g, int sbits, int labits, Item &it) {
   const int n = DIR == 0 ? g.nx : (DIR == 1 ? g.ny : g.nz);
-  const long nlines = DIR == 0 ? (long)g.nz * g.ny : (DIR == 1 ? (long)g.nz * g.nx : (long)g.ny * g.nx);
-  if (item >= (long)netile * nseg * nlines) return false;
-  const int et = (int)(item % netile);
-  long r = item / netile;
-  const int seg = (int)(r % nseg);
-  const long line = r / nseg;
-  it.e = et * 32 + (threadIdx.x & 31);
+  const int la_count = DIR == 2 ? g.ny : g.nz;
+  const unsigned z = blockIdx.z;
+  const int seg = (int)(z & ((1u << sbits) - 1u));
+  it.la = (int)((z >> sbits) & ((1u << labits) - 1u)) * LA_LINES;
+  it.tr = (int)(z >> (sbits + labits));
+  it.lb = (int)blockIdx.y * LB_LINES;
+  if (it.la >= la_count) return false;
+  it.e = (int)blockIdx.x * 32 + (int)(threadIdx.x & 31);
   if (it.e >= g.nens) return false;
-  it.c0 = (int)((long)seg * n / nseg);
-  it.c1 = (int)((long)(seg + 1) * n / nseg);
-  if (DIR == 0) {        // line = k*ny + j
-    it.la = (int)(line / g.ny); it.lb = (int)(line % g.ny);
-    it.base = (((long)it.la * g.ny + it.lb) * g.nx) * g.nens + it.e;
-  } else if (DIR == 1) { // line = k*nx + i
-    it.la = (int)(line / g.nx); it.lb = (int)(line % g.nx);
-    it.base = (((long)it.la * g.ny) * g.nx + it.lb) * g.nens + it.e;
-  } else {               // line = j*nx + i
-    it.la = (int)(line / g.nx); it.lb = (int)(line % g.nx);
-    it.base = ((long)it.la * g.nx + it.lb) * g.nens + it.e;
-  }
+  it.c0 = (seg * n) >> sbits;
+  it.c1 = ((seg + 1) * n) >> sbits;
+  if (DIR == 0) it.base = (((long)it.la * g.ny + it.lb) * g.nx) * g.nens + it.e;          // (k,j)
+  else if (DIR == 1) it.base = (((long)it.la * g.ny) * g.nx + it.lb) * g.nens + it.e;     // (k,i)
+  else it.base = ((long)it.la * g.nx + it.lb) * g.nens + it.e;                             // (j,i)
   return true;
 }
 

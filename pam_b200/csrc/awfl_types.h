@@ -31,7 +31,7 @@ struct SweepArgs {
   long vst;               // element stride of vtab: nens (member-dependent grid) or 1 (shared grid)
   double a, b, c;         // SSPRK3 stage coefficients (c = b*dt)
   int first;              // 1: this is the first sweep of the stage (tend is written, not accumulated)
-  int nseg;
+  int sbits, labits;      // grid encoding (decode_item): 2^sbits segments per line, labits bits for the first line index
 };
 
 // Tracer march arguments (k_march_tracer)
@@ -41,8 +41,7 @@ struct TracerSweepArgs {
   double *tflux;        // nt fields of interface fluxes for this direction
   const double *vtab;
   long vst;             // element stride of vtab: nens or 1
-  int nseg;
-  long items_per_tracer;
+  int sbits, labits;    // grid encoding (decode_item)
 };
 
 // declare_current_profile_as_hydrostatic arguments
@@ -57,8 +56,8 @@ struct HydroArgs {
 // Per-order launchers, defined in awfl_ord.cu (one translation unit per reconstruction order so they build in parallel).
 template <int ORD> struct OrdLaunch {
   // cell-centred marching kernels (awfl_march.cuh); vt: 0 constant horizontal, 1 constant-bank vertical, 2 global vertical
-  static void march_state(cudaStream_t s, const Geom &g, const Phys &ph, const SweepArgs &a, int dir, int mode, int vt, long items);
-  static void march_tracer(cudaStream_t s, const Geom &g, const TracerSweepArgs &a, int dir, int vt, long items);
+  static void march_state(cudaStream_t s, const Geom &g, const Phys &ph, const SweepArgs &a, int dir, int mode, int vt);
+  static void march_tracer(cudaStream_t s, const Geom &g, const TracerSweepArgs &a, int dir, int vt);
   static int upload_cvtab(cudaStream_t s, const double *host, size_t ndoubles);   // returns a cudaError_t
   static size_t cvtab_capacity();
   static void hydro_pint(cudaStream_t s, const Geom &g, const Phys &ph, const HydroArgs &a, bool shared);

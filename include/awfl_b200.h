@@ -99,6 +99,22 @@ double *awfl_variable_gravity(awfl_handle *h);
 const double *awfl_vert_sten_to_coefs(awfl_handle *h);
 const double *awfl_vert_weno_recon_lower(awfl_handle *h);
 
+/* The shim keeps the DataManager entries as the source of truth, like the reference (which fetches "variable_gravity"
+ * from the DataManager in every compute_tendencies call, Dycore.h:277): awfl_set_variable_gravity copies a caller-owned
+ * device array (nz,nens) into the handle before a step; awfl_export_tables copies the handle's variable_gravity,
+ * vert_sten_to_coefs and vert_weno_recon_lower into caller-owned device arrays (any pointer may be NULL). Both are
+ * device-to-device copies on the handle's stream. */
+int awfl_set_variable_gravity(awfl_handle *h, const double *variable_gravity);
+int awfl_export_tables(awfl_handle *h, double *variable_gravity, double *vert_sten_to_coefs, double *vert_weno_recon_lower);
+
+/* Small runtime helpers so that a host shim needs no CUDA header of its own: synchronous device-to-host /
+ * host-to-device copies (used at init for the (nz,nens) vertical grid and by tests) and the current device ordinal. */
+int awfl_copy_to_host(void *dst_host, const void *src_device, unsigned long bytes);
+int awfl_copy_to_device(void *dst_device, const void *src_host, unsigned long bytes);
+int awfl_current_device(void);
+int awfl_device_alloc(void **ptr, unsigned long bytes);   /* zero-filled device memory */
+void awfl_device_free(void *ptr);
+
 /* Resolved option value by name ("R_d","cp_d","R_v","cp_v","p0","grav","cv_d","gamma_d","kappa_d","C0"); NaN if unknown. */
 double awfl_get_option(const awfl_handle *h, const char *name);
 

@@ -683,6 +683,38 @@ double *awfl_variable_gravity(awfl_handle *h) { return h->grav_var; }
 const double *awfl_vert_sten_to_coefs(awfl_handle *h) { return h->vs2c; }
 const double *awfl_vert_weno_recon_lower(awfl_handle *h) { return h->vwrl; }
 
+int awfl_copy_to_host(void *dst_host, const void *src_device, unsigned long bytes) {
+  return cudaMemcpy(dst_host, src_device, bytes, cudaMemcpyDeviceToHost) == cudaSuccess ? 0 : 1;
+}
+int awfl_copy_to_device(void *dst_device, const void *src_host, unsigned long bytes) {
+  return cudaMemcpy(dst_device, src_host, bytes, cudaMemcpyHostToDevice) == cudaSuccess ? 0 : 1;
+}
+int awfl_device_alloc(void **ptr, unsigned long bytes) {
+  if (cudaMalloc(ptr, bytes) != cudaSuccess) { *ptr = nullptr; return 1; }
+  return cudaMemset(*ptr, 0, bytes) == cudaSuccess ? 0 : 1;
+}
+void awfl_device_free(void *ptr) { if (ptr) cudaFree(ptr); }
+int awfl_current_device(void) {
+  int d = 0;
+  return cudaGetDevice(&d) == cudaSuccess ? d : 0;
+}
+
+int awfl_set_variable_gravity(awfl_handle *h, const double *variable_gravity) {
+  if (!variable_gravity) return fail(h, "awfl_set_variable_gravity: NULL pointer");
+  if (variable_gravity == h->grav_var) return 0;
+  CK(cudaMemcpyAsync(h->grav_var, variable_gravity, sizeof(double) * h->g.nz * h->g.nens, cudaMemcpyDeviceToDevice, h->stream));
+  return 0;
+}
+
+int awfl_export_tables(awfl_handle *h, double *variable_gravity, double *vert_sten_to_coefs, double *vert_weno_recon_lower) {
+  const Geom &g = h->g;
+  const size_t o = h->ord, hs = h->hs, lv = (size_t)(g.nz + 2) * g.nens;
+  if (variable_gravity) CK(cudaMemcpyAsync(variable_gravity, h->grav_var, sizeof(double) * g.nz * g.nens, cudaMemcpyDeviceToDevice, h->stream));
+  if (vert_sten_to_coefs) CK(cudaMemcpyAsync(vert_sten_to_coefs, h->vs2c, sizeof(double) * lv * o * o, cudaMemcpyDeviceToDevice, h->stream));
+  if (vert_weno_recon_lower) CK(cudaMemcpyAsync(vert_weno_recon_lower, h->vwrl, sizeof(double) * lv * hs * hs * hs, cudaMemcpyDeviceToDevice, h->stream));
+  return 0;
+}
+
 int awfl_compute_time_step(awfl_handle *h, const awfl_fields *f, double cfl, double *dt_host) {
   FieldPtrs fp;
   if (make_field_ptrs(h, f, fp)) return 1;

@@ -1,0 +1,194 @@
+// Dycore.h -- drop-in replacement for E3SM-Project/PAM's dynamics/awfl/Dycore.h (class Dycore, lines 13-1550).
+//
+// A PAM build selects its dycore by directory (`-DPAM_DYCORE=<dir>`, dynamics/CMakeLists.txt:5-17): point it at this
+// directory and link libawfl_b200.so. The class below keeps the reference's public method names, argument meaning and
+// error behaviour; every compute method pulls raw device pointers out of the coupler's DataManager and calls the C ABI
+// of include/awfl_b200.h, whose entry points launch hand-written sm_100a kernels. There is no YAKL parallel_for and no
+// CPU fallback behind this header.
+//
+// The class is templated on the coupler type so that it accepts both the real `pam::PamCoupler` (YAKL-backed
+// DataManager: `dm.get<real,4>(name).data()`) and the header-only look-alike of pam_coupler_b200.h (cudaMalloc-backed).
+// Required coupler surface (pam_core/pam_coupler.h:59-251): get_nx/ny/nz/nens, get_xlen/ylen, get_option<T>,
+// set_option<T>, option_exists, get_tracer_names, get_tracer_info, get_num_tracers,
+// get_data_manager_device_readwrite/readonly with get<T,N>(name) -> array with .data(), register_and_allocate<T>,
+// entry_exists.
+#pragma once
+#include <cstdio>
+#include <string>
+#include <vector>
+
+#include "../../include/awfl_b200.h"
+
+#ifndef PAM_B200_REAL_DEFINED
+#define PAM_B200_REAL_DEFINED
+typedef double real;   // pam_core/pam_const.h:22
+#endif
+
+namespace awfl_b200_detail {
+// pam_core/pam_const.h:249-252: print, then throw the message
+[[noreturn]] inline void endrun(const std::string &msg) {
+  std::fprintf(stderr, "%s\n", msg.c_str());
+  throw std::string(msg);
+}
+}  // namespace awfl_b200_detail
+
+class Dycore {
+ public:
+  // The reference fixes the order at compile time with MW_ORD (Dycore.h:17-21); the same macro is honoured here.
+#ifdef MW_ORD
+  static int const ord = MW_ORD;
+#else
+  static int const ord = 5;
+#endif
+  static int const hs = (ord + 1) / 2;
+  static int const num_state = 5;
+  static int const idR = 0, idU = 1, idV = 2, idW = 3, idT = 4;
+
+  Dycore() : h_(nullptr), nt_(0) {}
+  ~Dycore() { release(); }
+  Dycore(const Dycore &) = delete;
+  Dycore &operator=(const Dycore &) = delete;
+
+  // Dycore::dycore_name (Dycore.h:1544)
+  const char *dycore_name() const { return awfl_dycore_name(); }
+
+  // Dycore::init (Dycore.h:835-1091)
+  template <class Coupler>
+  void init(Coupler &coupler, bool verbose = false) {
+    using awfl_b200_detail::endrun;
+    (void)verbose;
+    release();
+    const int nz = coupler.get_nz(), ny = coupler.get_ny(), nx = coupler.get_nx(), nens = coupler.get_nens();
+    coupler.template set_option<bool>("balance_hydrostasis_with_gravity", true);             // Dycore.h:866
+    set_default<real>(coupler, "R_d", 287.);  set_default<real>(coupler, "cp_d", 1003.);     // Dycore.h:871-876
+    set_default<real>(coupler, "R_v", 461.);  set_default<real>(coupler, "cp_v", 1859.);
+    set_default<real>(coupler, "p0", 1.e5);   set_default<real>(coupler, "grav", 9.81);
+    const std::vector<std::string> names = coupler.get_tracer_names();
+    nt_ = (int)names.size();
+    std::vector<unsigned char> pos(nt_ > 0 ? nt_ : 1), adds(nt_ > 0 ? nt_ : 1);
+    int idWV = -1;
+    for (int t = 0; t < nt_; t++) {                                                          // Dycore.h:952-981
+      std::string desc; bool found = false, p = false, a = false;
+      coupler.get_tracer_info(names[t], desc, found, p, a);
+      pos[t] = p; adds[t] = a;
+      if (names[t] == "water_vapor") idWV = t;
+    }
+    if (idWV < 0) endrun("ERROR: the AWFL dycore needs a tracer named water_vapor (Dycore.h:83,974)");
+    auto &dm = coupler.get_data_manager_device_readwrite();
+    std::vector<double> dz((size_t)nz * nens);
+    if (awfl_copy_to_host(dz.data(), dm.template get<real const, 2>("vertical_cell_dz").data(), sizeof(double) * dz.size()))
+      endrun("ERROR: could not read vertical_cell_dz from the device");
+    awfl_config cfg{};
+    cfg.nz = nz; cfg.ny = ny; cfg.nx = nx; cfg.nens = nens; cfg.num_tracers = nt_; cfg.ord = ord;
+    cfg.xlen = coupler.get_xlen(); cfg.ylen = coupler.get_ylen();
+    cfg.R_d = coupler.template get_option<real>("R_d");   cfg.cp_d = coupler.template get_option<real>("cp_d");
+    cfg.R_v = coupler.template get_option<real>("R_v");   cfg.cp_v = coupler.template get_option<real>("cp_v");
+    cfg.p0 = coupler.template get_option<real>("p0");     cfg.grav = coupler.template get_option<real>("grav");
+    cfg.gamma_d = coupler.option_exists("gamma_d") ? coupler.template get_option<real>("gamma_d") : 0.;
+    cfg.kappa_d = coupler.option_exists("kappa_d") ? coupler.template get_option<real>("kappa_d") : 0.;
+    cfg.C0 = coupler.option_exists("C0") ? coupler.template get_option<real>("C0") : 0.;
+    cfg.idWV = idWV; cfg.tracer_positive = pos.data(); cfg.tracer_adds_mass = adds.data();
+    cfg.dz_host = dz.data(); cfg.device = current_device(); cfg.stream = nullptr;   // YAKL's default stream
+    if (awfl_create(&cfg, &h_) != 0) endrun(std::string("awfl_create: ") + awfl_last_error(nullptr));
+    // options the reference sets if absent (Dycore.h:883-891,974)
+    set_default<real>(coupler, "cv_d", awfl_get_option(h_, "cv_d"));
+    set_default<real>(coupler, "gamma_d", awfl_get_option(h_, "gamma_d"));
+    set_default<real>(coupler, "kappa_d", awfl_get_option(h_, "kappa_d"));
+    set_default<real>(coupler, "cv_v", coupler.template get_option<real>("R_v") - coupler.template get_option<real>("cp_v"));   // Dycore.h:886 (sic)
+    set_default<real>(coupler, "C0", awfl_get_option(h_, "C0"));
+    coupler.template set_option<int>("idWV", idWV);
+    // dycore-owned DataManager entries other modules may read (Dycore.h:868,897-898,975-984)
+    if (!dm.entry_exists("variable_gravity")) dm.template register_and_allocate<real>("variable_gravity", "", {nz, nens});
+    if (!dm.entry_exists("vert_sten_to_coefs")) dm.template register_and_allocate<real>("vert_sten_to_coefs", "", {nz + 2, ord, ord, nens});
+    if (!dm.entry_exists("vert_weno_recon_lower")) dm.template register_and_allocate<real>("vert_weno_recon_lower", "", {nz + 2, hs, hs, hs, nens});
+    if (!dm.entry_exists("hy_dens_cells")) dm.template register_and_allocate<real>("hy_dens_cells", "", {nz, nens});
+    if (!dm.entry_exists("hy_pressure_cells")) dm.template register_and_allocate<real>("hy_pressure_cells", "", {nz, nens});
+    check(awfl_export_tables(h_, dm.template get<real, 2>("variable_gravity").data(), dm.template get<real, 4>("vert_sten_to_coefs").data(),
+                             dm.template get<real, 5>("vert_weno_recon_lower").data()), "awfl_export_tables");
+  }
+
+  // Dycore::timeStep (Dycore.h:107-255)
+  template <class Coupler>
+  void timeStep(Coupler &coupler) {
+    Fields<Coupler> f(coupler, nt_);
+    auto &dm = coupler.get_data_manager_device_readwrite();
+    check(awfl_set_variable_gravity(h_, dm.template get<real const, 2>("variable_gravity").data()), "awfl_set_variable_gravity");
+    check(awfl_time_step(h_, &f.f, coupler.template get_option<real>("crm_dt"), 0, nullptr), "awfl_time_step");
+  }
+
+  // Dycore::compute_time_step (Dycore.h:65-102)
+  template <class Coupler>
+  real compute_time_step(Coupler &coupler, real cfl_in = 0.8) {
+    Fields<Coupler> f(coupler, nt_);
+    double dt = 0.;
+    check(awfl_compute_time_step(h_, &f.f, cfl_in, &dt), "awfl_compute_time_step");
+    return dt;
+  }
+
+  // Dycore::declare_current_profile_as_hydrostatic (Dycore.h:1392-1504)
+  template <class Coupler>
+  void declare_current_profile_as_hydrostatic(Coupler &coupler, bool use_gcm_data = false) {
+    Fields<Coupler> f(coupler, nt_);
+    auto &dm = coupler.get_data_manager_device_readwrite();
+    awfl_gcm_columns g{};
+    if (use_gcm_data) {                                                                      // Dycore.h:1416-1420
+      g.gcm_density_dry = dm.template get<real const, 2>("gcm_density_dry").data();
+      g.gcm_temp = dm.template get<real const, 2>("gcm_temp").data();
+      g.gcm_water_vapor = dm.template get<real const, 2>("gcm_water_vapor").data();
+      g.gcm_cloud_water = dm.template get<real const, 2>("gcm_cloud_water").data();
+      g.gcm_cloud_ice = dm.template get<real const, 2>("gcm_cloud_ice").data();
+    }
+    check(awfl_declare_hydrostatic(h_, &f.f, use_gcm_data ? &g : nullptr), "awfl_declare_hydrostatic");
+    check(awfl_export_tables(h_, dm.template get<real, 2>("variable_gravity").data(), nullptr, nullptr), "awfl_export_tables");
+  }
+
+  // Dycore::compute_mass (Dycore.h:37-60): returns (num_tracers+2) x nens means of q*dz, host memory, row-major
+  template <class Coupler>
+  std::vector<real> compute_mass(Coupler &coupler) {
+    Fields<Coupler> f(coupler, nt_);
+    std::vector<real> out((size_t)(nt_ + 2) * coupler.get_nens());
+    check(awfl_compute_mass(h_, &f.f, out.data()), "awfl_compute_mass");
+    return out;
+  }
+
+  // Dycore::finalize (Dycore.h:1548)
+  template <class Coupler>
+  void finalize(Coupler & /*coupler*/) { release(); }
+
+  awfl_handle *handle() { return h_; }
+
+ private:
+  awfl_handle *h_;
+  int nt_;
+
+  // the coupler's prognostic fields as raw device pointers (pam_coupler.h:259-263 + tracers)
+  template <class Coupler>
+  struct Fields {
+    awfl_fields f;
+    std::vector<double *> tr;
+    Fields(Coupler &c, int nt) : tr(nt > 0 ? nt : 1) {
+      auto &dm = c.get_data_manager_device_readwrite();
+      f.density_dry = dm.template get<real, 4>("density_dry").data();
+      f.uvel = dm.template get<real, 4>("uvel").data();
+      f.vvel = dm.template get<real, 4>("vvel").data();
+      f.wvel = dm.template get<real, 4>("wvel").data();
+      f.temp = dm.template get<real, 4>("temp").data();
+      const std::vector<std::string> names = c.get_tracer_names();
+      if ((int)names.size() != nt) awfl_b200_detail::endrun("ERROR: tracers were added after Dycore::init");
+      for (int t = 0; t < nt; t++) tr[t] = dm.template get<real, 4>(names[t]).data();
+      f.tracers = tr.data();
+    }
+  };
+
+  template <class T, class Coupler>
+  static void set_default(Coupler &c, const char *key, T v) {
+    if (!c.option_exists(key)) c.template set_option<T>(key, v);
+  }
+  void check(int rc, const char *what) {
+    if (rc != 0) awfl_b200_detail::endrun(std::string(what) + ": " + awfl_last_error(h_));
+  }
+  void release() {
+    if (h_) { awfl_destroy(h_); h_ = nullptr; }
+  }
+  static int current_device() { return awfl_current_device(); }
+};

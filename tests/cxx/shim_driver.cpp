@@ -1,0 +1,104 @@
+// Test driver for the C++ host shim (pam_b200/cxx/Dycore.h + pam_coupler_b200.h): the same call sequence as the
+// reference's standalone driver (standalone/mmf_simplified/driver.cpp:120-285) -- set options, allocate_coupler_state,
+// set_grid, add tracers, dycore.init, then coupler.run_module("dycore", [&](auto &c){ dycore.timeStep(c); }).
+//   shim_driver selftest            no GPU needed: names, DataManager/Options errors, init must fail loudly without a GPU
+//   shim_driver run IN OUT NSTEPS   reads a case written by tests/test_cxx_shim.py, steps it, writes the fields back
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "pam_coupler_b200.h"
+
+using pam_b200::PamCoupler;
+
+static int selftest() {
+  Dycore dycore;
+  if (std::string(dycore.dycore_name()) != "SSPRK3+WENO+FV A-grid") { std::printf("FAIL name\n"); return 1; }
+  pam_b200::Options o;
+  o.set_option<real>("crm_dt", 2.0);
+  if (o.get_option<real>("crm_dt") != 2.0 || !o.option_exists("crm_dt")) { std::printf("FAIL options\n"); return 1; }
+  int caught = 0;
+  try { o.get_option<real>("absent"); } catch (std::string &s) { caught++; }
+  try { o.get_option<int>("crm_dt"); } catch (std::string &s) { caught++; }
+  if (caught != 2) { std::printf("FAIL option errors\n"); return 1; }
+  // Without a device every allocation fails: the coupler must report it (endrun), never fall back to host memory.
+  PamCoupler c;
+  bool device_ok = true;
+  try { c.allocate_coupler_state(8, 1, 8, 2); } catch (std::string &s) { device_ok = false; }
+  if (!device_ok) { std::printf("selftest ok (no device: allocation refused loudly)\n"); return 0; }
+  // With a device: DataManager error behaviour and a full init
+  caught = 0;
+  try { c.get_data_manager_device_readwrite().get<real, 4>("nope"); } catch (std::string &s) { caught++; }
+  try { c.get_data_manager_device_readwrite().get<real, 3>("uvel"); } catch (std::string &s) { caught++; }
+  try { c.get_data_manager_device_readwrite().get<int, 4>("uvel"); } catch (std::string &s) { caught++; }
+  if (caught != 3) { std::printf("FAIL DataManager errors\n"); return 1; }
+  try { Dycore d; d.init(c); std::printf("FAIL init accepted a coupler without water_vapor\n"); return 1; } catch (std::string &s) {}
+  std::printf("selftest ok (device present)\n");
+  return 0;
+}
+
+static void rd(FILE *f, void *p, size_t n) { if (std::fread(p, 1, n, f) != n) { std::printf("short read\n"); std::exit(2); } }
+
+static int run(const char *in, const char *out, int nsteps) {
+  FILE *f = std::fopen(in, "rb");
+  if (!f) { std::printf("cannot open %s\n", in); return 2; }
+  int hdr[6];   // nz ny nx nens nt use_default_consts
+  rd(f, hdr, sizeof(hdr));
+  const int nz = hdr[0], ny = hdr[1], nx = hdr[2], nens = hdr[3], nt = hdr[4];
+  double par[9];   // xlen ylen crm_dt R_d cp_d R_v cp_v p0 grav
+  rd(f, par, sizeof(par));
+  std::vector<double> zint(nz + 1);
+  rd(f, zint.data(), sizeof(double) * (nz + 1));
+  std::vector<std::string> tnames(nt);
+  std::vector<int> tpos(nt), tadds(nt);
+  for (int t = 0; t < nt; t++) {
+    char name[32]; int flags[2];
+    rd(f, name, 32); rd(f, flags, sizeof(flags));
+    tnames[t] = name; tpos[t] = flags[0]; tadds[t] = flags[1];
+  }
+  PamCoupler coupler;
+  coupler.set_option<real>("crm_dt", par[2]);
+  if (!hdr[5]) {
+    coupler.set_option<real>("R_d", par[3]); coupler.set_option<real>("cp_d", par[4]); coupler.set_option<real>("R_v", par[5]);
+    coupler.set_option<real>("cp_v", par[6]); coupler.set_option<real>("p0", par[7]); coupler.set_option<real>("grav", par[8]);
+  }
+  coupler.allocate_coupler_state(nz, ny, nx, nens);
+  coupler.set_grid(par[0], par[1], zint);
+  for (int t = 0; t < nt; t++) coupler.add_tracer(tnames[t], tnames[t], tpos[t] != 0, tadds[t] != 0);   // micro/sgs register first (driver.cpp:189-191)
+  Dycore dycore;
+  dycore.init(coupler);
+  std::vector<std::string> names = {"density_dry", "uvel", "vvel", "wvel", "temp"};
+  for (auto &n : tnames) names.push_back(n);
+  const size_t ncell = (size_t)nz * ny * nx * nens;
+  std::vector<double> buf(ncell);
+  auto &dm = coupler.get_data_manager_device_readwrite();
+  for (auto &n : names) { rd(f, buf.data(), sizeof(double) * ncell); dm.write<real>(n, buf.data()); }
+  std::fclose(f);
+  dycore.declare_current_profile_as_hydrostatic(coupler);
+  const double dt_cfl = dycore.compute_time_step(coupler);
+  for (int s = 0; s < nsteps; s++) coupler.run_module("dycore", [&](PamCoupler &c) { dycore.timeStep(c); });   // driver.cpp:248
+  std::vector<real> mass = dycore.compute_mass(coupler);
+  FILE *g = std::fopen(out, "wb");
+  std::fwrite(&dt_cfl, sizeof(double), 1, g);
+  std::vector<double> gv((size_t)nz * nens);
+  dm.read<real>("variable_gravity", gv.data());
+  std::fwrite(gv.data(), sizeof(double), gv.size(), g);
+  std::fwrite(mass.data(), sizeof(double), mass.size(), g);
+  for (auto &n : names) { dm.read<real>(n, buf.data()); std::fwrite(buf.data(), sizeof(double), ncell, g); }
+  std::fclose(g);
+  dycore.finalize(coupler);
+  coupler.finalize();
+  std::printf("shim_driver: %d steps of %s done\n", nsteps, dycore.dycore_name());
+  return 0;
+}
+
+int main(int argc, char **argv) {
+  try {
+    if (argc >= 2 && !std::strcmp(argv[1], "selftest")) return selftest();
+    if (argc >= 5 && !std::strcmp(argv[1], "run")) return run(argv[2], argv[3], std::atoi(argv[4]));
+  } catch (std::string &s) { std::printf("endrun: %s\n", s.c_str()); return 3; }
+  std::printf("usage: shim_driver selftest | run IN OUT NSTEPS\n");
+  return 64;
+}

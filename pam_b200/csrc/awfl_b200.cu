@@ -35,48 +35,56 @@ struct FctArgs {
   const double *tfx, *tfy, *tfz;
   const double *fct_start;  // explicit start mass (tendency entry point) or NULL
   double *mult;           // nt fields
-  const double *dz;
+  const double *dz, *rdz;
   const unsigned char *positive;
   double sa, sb;          // start = sa*T0 + sb*Ts
   double dt;
+  double rdx, rdy;
 };
 
-__device__ __forceinline__ void cell_coords(long cell, const Geom &g, int &k, int &j, int &i, int &e) {
-  e = (int)(cell % g.nens); long r = cell / g.nens;
-  i = (int)(r % g.nx); r /= g.nx;
-  j = (int)(r % g.ny); k = (int)(r / g.ny);
+// Work decomposition of the two cell-local tracer kernels: blockIdx.x = (k*ny + j)*rblocks + rb, where the rblocks
+// blocks of a row cover its nx*nens (i, member) pairs; blockIdx.y = tracer. Every index is 32-bit and the row part is
+// block-uniform (the first version decoded a 64-bit linear cell index with three runtime divisions per thread and was
+// issue-bound at a third of the HBM rate: profiles/r01d, 2.7 ms per launch at NT=10).
+struct RowMap { int rblocks, rowlen; };
+__device__ __forceinline__ bool row_coords(const Geom &g, const RowMap m, long &cell, int &k, int &j, int &i, int &e) {
+  const unsigned kj = blockIdx.x / (unsigned)m.rblocks, rb = blockIdx.x - kj * (unsigned)m.rblocks;
+  const int r = (int)(rb * blockDim.x + threadIdx.x);
+  k = (int)(kj / (unsigned)g.ny); j = (int)(kj - (unsigned)k * (unsigned)g.ny);
+  i = (int)((unsigned)r / (unsigned)g.nens); e = r - i * g.nens;
+  cell = (long)kj * m.rowlen + r;
+  return r < m.rowlen;
 }
 
-__global__ void __launch_bounds__(256) k_fct_mult(const Geom g, const FctArgs a) {
-  const long cell = (long)blockIdx.x * blockDim.x + threadIdx.x;
+__global__ void __launch_bounds__(256) k_fct_mult(const Geom g, const FctArgs a, const RowMap rm) {
+  long cell; int k, j, i, e;
+  if (!row_coords(g, rm, cell, k, j, i, e)) return;
   const int tr = blockIdx.y;
-  if (cell >= g.ncell) return;
   const long nc = g.ncell;
   double mult = 1.0;
   if (a.positive[tr]) {
-    int k, j, i, e;
-    cell_coords(cell, g, k, j, i, e);
     const long sx = g.nens, sy = (long)g.nx * g.nens, sz = (long)g.ny * g.nx * g.nens;
-    const double dzk = __ldg(a.dz + (long)k * g.nens + e);
+    const double dzk = __ldg(a.dz + (long)k * g.nens + e), rdzk = __ldg(a.rdz + (long)k * g.nens + e);
     double start;
     if (a.fct_start) start = __ldg(a.fct_start + tr * nc + cell);
     else {
       start = __ldg(a.q0 + (NS + tr) * nc + cell);
       if (a.sb != 0.0) start = a.sa * start + a.sb * __ldg(a.qs + (NS + tr) * nc + cell);
     }
-    const double avail = fmax(start, 0.0) * g.dx * g.dy * dzk;
-    const double *fx = a.tfx + tr * nc, *fz = a.tfz + tr * (nc + nc / g.nz);
+    const double vol = g.dx * g.dy * dzk;
+    const double avail = fmax(start, 0.0) * vol;
+    const double *fx = a.tfx + tr * nc, *fz = a.tfz + tr * (nc + sz);
     const double fx0 = __ldg(fx + cell), fx1 = __ldg(fx + (i == g.nx - 1 ? cell - (long)(g.nx - 1) * sx : cell + sx));
-    const double ox = (fmax(fx1, 0.0) - fmin(fx0, 0.0)) / g.dx;
+    const double ox = (fmax(fx1, 0.0) - fmin(fx0, 0.0)) * a.rdx;
     double oy = 0.0;
     if (!g.sim2d) {
       const double *fy = a.tfy + tr * nc;
       const double fy0 = __ldg(fy + cell), fy1 = __ldg(fy + (j == g.ny - 1 ? cell - (long)(g.ny - 1) * sy : cell + sy));
-      oy = (fmax(fy1, 0.0) - fmin(fy0, 0.0)) / g.dy;
+      oy = (fmax(fy1, 0.0) - fmin(fy0, 0.0)) * a.rdy;
     }
     const double fz0 = __ldg(fz + cell), fz1 = __ldg(fz + cell + sz);
-    const double oz = (fmax(fz1, 0.0) - fmin(fz0, 0.0)) / dzk;
-    const double out = (ox + oy + oz) * a.dt * g.dx * g.dy * dzk;
+    const double oz = (fmax(fz1, 0.0) - fmin(fz0, 0.0)) * rdzk;
+    const double out = (ox + oy + oz) * a.dt * vol;
     if (out > avail) mult = avail / out;
   }
   a.mult[tr * nc + cell] = mult;
@@ -87,9 +95,10 @@ __global__ void __launch_bounds__(256) k_fct_mult(const Geom g, const FctArgs a)
 struct TracerUpdArgs {
   const double *q0, *qs;  // step-start and stage-input state (N fields)
   double *qout;           // stage output state (N fields) or tracer tendencies (nt fields) when tend_only
-  const double *tfx, *tfy, *tfz, *mult, *dz;
+  const double *tfx, *tfy, *tfz, *mult, *rdz;
   const unsigned char *positive;
   double a, b, c;
+  double rdx, rdy;
   int tend_only;
 };
 
@@ -100,23 +109,21 @@ __device__ __forceinline__ double fct_scaled(double F, double mult_lo, double mu
   return F;   // periodic seam with F<0: min() of the two edge copies selects the unscaled one (Dycore.h:574-579)
 }
 
-__global__ void __launch_bounds__(256) k_tracer_update(const Geom g, const TracerUpdArgs a) {
-  const long cell = (long)blockIdx.x * blockDim.x + threadIdx.x;
+__global__ void __launch_bounds__(256) k_tracer_update(const Geom g, const TracerUpdArgs a, const RowMap rm) {
+  long cell; int k, j, i, e;
+  if (!row_coords(g, rm, cell, k, j, i, e)) return;
   const int tr = blockIdx.y;
-  if (cell >= g.ncell) return;
   const long nc = g.ncell;
-  int k, j, i, e;
-  cell_coords(cell, g, k, j, i, e);
   const long sx = g.nens, sy = (long)g.nx * g.nens, sz = (long)g.ny * g.nx * g.nens;
-  const double *fx = a.tfx + tr * nc, *fz = a.tfz + tr * (nc + nc / g.nz), *mu = a.mult + tr * nc;
-  const double dzk = __ldg(a.dz + (long)k * g.nens + e);
+  const double *fx = a.tfx + tr * nc, *fz = a.tfz + tr * (nc + sz), *mu = a.mult + tr * nc;
+  const double rdzk = __ldg(a.rdz + (long)k * g.nens + e);
   const double m_c = __ldg(mu + cell);
   // x faces
   const long cxm = i == 0 ? cell + (long)(g.nx - 1) * sx : cell - sx;
   const long cxp = i == g.nx - 1 ? cell - (long)(g.nx - 1) * sx : cell + sx;
   const double f0 = fct_scaled(__ldg(fx + cell), __ldg(mu + cxm), m_c, i == 0);
   const double f1 = fct_scaled(__ldg(fx + cxp), m_c, __ldg(mu + cxp), i == g.nx - 1);
-  double tend = -(f1 - f0) / g.dx;
+  double tend = -(f1 - f0) * a.rdx;
   // y faces
   if (!g.sim2d) {
     const double *fy = a.tfy + tr * nc;
@@ -124,12 +131,12 @@ __global__ void __launch_bounds__(256) k_tracer_update(const Geom g, const Trace
     const long cyp = j == g.ny - 1 ? cell - (long)(g.ny - 1) * sy : cell + sy;
     const double g0 = fct_scaled(__ldg(fy + cell), __ldg(mu + cym), m_c, j == 0);
     const double g1 = fct_scaled(__ldg(fy + cyp), m_c, __ldg(mu + cyp), j == g.ny - 1);
-    tend -= (g1 - g0) / g.dy;
+    tend -= (g1 - g0) * a.rdy;
   }
   // z faces (walls carry zero flux)
   const double h0 = fct_scaled(__ldg(fz + cell), k > 0 ? __ldg(mu + cell - sz) : 1.0, m_c, false);
   const double h1 = fct_scaled(__ldg(fz + cell + sz), m_c, k < g.nz - 1 ? __ldg(mu + cell + sz) : 1.0, false);
-  tend -= (h1 - h0) / dzk;
+  tend -= (h1 - h0) * rdzk;
   if (a.tend_only) { a.qout[tr * nc + cell] = tend; return; }
   const double ts = __ldg(a.qs + (NS + tr) * nc + cell);
   double v = a.b * ts;
@@ -534,15 +541,17 @@ static void run_stage(awfl_handle *h, const double *qin, const double *q0, doubl
     launch_tracer_sweep(h, dir, t);
   }
   if (g.nt > 0) {
-    const unsigned blocks = (unsigned)((g.ncell + 255) / 256);
+    RowMap rm;
+    rm.rowlen = g.nx * g.nens; rm.rblocks = (rm.rowlen + 255) / 256;
+    const unsigned blocks = (unsigned)rm.rblocks * (unsigned)(g.nz * g.ny);
     FctArgs f;
     f.q0 = q0; f.qs = qin; f.tfx = h->tflux[0]; f.tfy = h->tflux[1]; f.tfz = h->tflux[2]; f.fct_start = fct_start;
-    f.mult = h->mult; f.dz = h->dz; f.positive = h->positive_d; f.sa = sa; f.sb = sb; f.dt = dt_stage;
-    { ProfScope ps(h, KC_FCT); k_fct_mult<<<dim3(blocks, g.nt), 256, 0, h->stream>>>(g, f); }
+    f.mult = h->mult; f.dz = h->dz; f.rdz = h->rdz; f.rdx = 1.0 / g.dx; f.rdy = 1.0 / g.dy; f.positive = h->positive_d; f.sa = sa; f.sb = sb; f.dt = dt_stage;
+    { ProfScope ps(h, KC_FCT); k_fct_mult<<<dim3(blocks, g.nt), 256, 0, h->stream>>>(g, f, rm); }
     TracerUpdArgs u;
     u.q0 = q0; u.qs = qin; u.qout = mode == 2 ? tr_out : qout; u.tfx = h->tflux[0]; u.tfy = h->tflux[1]; u.tfz = h->tflux[2];
-    u.mult = h->mult; u.dz = h->dz; u.positive = h->positive_d; u.a = a; u.b = b; u.c = b * dt_full; u.tend_only = mode == 2;
-    { ProfScope ps(h, KC_TRACER_UPD); k_tracer_update<<<dim3(blocks, g.nt), 256, 0, h->stream>>>(g, u); }
+    u.mult = h->mult; u.rdz = h->rdz; u.rdx = f.rdx; u.rdy = f.rdy; u.positive = h->positive_d; u.a = a; u.b = b; u.c = b * dt_full; u.tend_only = mode == 2;
+    { ProfScope ps(h, KC_TRACER_UPD); k_tracer_update<<<dim3(blocks, g.nt), 256, 0, h->stream>>>(g, u, rm); }
   }
 }
 
@@ -566,6 +575,9 @@ int awfl_create(const awfl_config *cfg, awfl_handle **out) {
   if (!cfg || cfg->nz < 1 || cfg->ny < 1 || cfg->nx < 1 || cfg->nens < 1 || cfg->num_tracers < 0) { g_create_err = "awfl_create: bad dimensions"; return 1; }
   if (cfg->ord != 3 && cfg->ord != 5 && cfg->ord != 7 && cfg->ord != 9) { g_create_err = "awfl_create: ord must be 3, 5, 7 or 9"; return 1; }
   const int hs0 = (cfg->ord + 1) / 2;
+  if ((long)cfg->nx * cfg->nens >= (1L << 31) || ((long)cfg->nx * cfg->nens + 255) / 256 * cfg->nz * cfg->ny >= (1L << 31)) {
+    g_create_err = "awfl_create: nx*nens and the block count of one field must fit 31 bits"; return 1;
+  }
   if (cfg->nx < hs0 || (cfg->ny > 1 && cfg->ny < hs0) || cfg->nz < hs0) { g_create_err = "awfl_create: each active dimension needs at least (ord+1)/2 cells"; return 1; }
   if (!cfg->dz_host) { g_create_err = "awfl_create: dz_host is NULL"; return 1; }
   if (cfg->num_tracers > 0 && (!cfg->tracer_positive || !cfg->tracer_adds_mass)) { g_create_err = "awfl_create: tracer flag arrays are NULL"; return 1; }

@@ -95,9 +95,17 @@ def cpu_reference_rate(w, seconds_target=12.0, warm=1, steps=None, nens=None):
     sample of the workload: same grid, order, tracers and inputs, fewer ensemble members. Returns the cpu_baseline dict
     and the per-step times."""
     from oracle import reflib
-    cores = os.cpu_count() or 1
-    os.environ.setdefault("OMP_NUM_THREADS", str(cores))
+    cores = int(os.environ.get("AWFL_REF_THREADS", "0")) or len(os.sched_getaffinity(0)) or os.cpu_count() or 1
+    # all the host threads the box offers: torchrun exports OMP_NUM_THREADS=1 to its workers, which is not what the
+    # reference arm is asked to measure, so the value is overridden here (before libgomp reads it) and again through
+    # omp_set_num_threads in case an OpenMP runtime is already initialised in this process
+    os.environ["OMP_NUM_THREADS"] = str(cores)
     os.environ.setdefault("OMP_PROC_BIND", "close")
+    try:
+        import ctypes
+        ctypes.CDLL("libgomp.so.1").omp_set_num_threads(cores)
+    except OSError:
+        pass
     kind = "reference"
     if not reflib.available(w["ord"], omp=True):
         raise RuntimeError("oracle/_ref/libpam_ref_ord%d_omp.so is missing (build it with __graft_entry__.build() where "
@@ -151,6 +159,7 @@ def main():
     ap.add_argument("--ord", type=int, default=None)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--host-slabs", type=int, default=0, help="member slabs pipelined by the host-buffer entry point (0 = library default)")
     args = ap.parse_args()
     w = dict(WORKLOADS[args.workload])
     if args.ord:
@@ -248,6 +257,8 @@ def main():
         for hbuf, n in zip(host, names):
             hbuf.copy_(init[n])
         harr = [hbuf.numpy() for hbuf in host]
+        if args.host_slabs > 0:
+            d.set_host_slabs(args.host_slabs)
         for _ in range(2):
             d.time_step_host(harr, CRM_DT)
         barrier()
@@ -265,7 +276,9 @@ def main():
         fb = 8 * ncell * len(names)
         e2e = {"value": float(eu.item()) / float(te.item()), "unit": "cell-updates/s", "h2d_bytes_per_step": fb * world,
                "d2h_bytes_per_step": fb * world, "steps": nst,
-               "note": "awfl_time_step_host: pinned host fields -> device, Dycore::timeStep, device -> host, every step"}
+               "host_slabs": args.host_slabs or 4,
+               "note": "awfl_time_step_host: pinned host fields -> device, Dycore::timeStep, device -> host, every step; the ensemble "
+                       "is pipelined in member slabs so that copies of one slab overlap the kernels of another"}
 
     if rank != 0:
         if world > 1:

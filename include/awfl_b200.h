@@ -75,6 +75,15 @@ int awfl_time_step(awfl_handle *h, const awfl_fields *f, double crm_dt, int ncyc
  * density_dry,uvel,vvel,wvel,temp, then the tracers. */
 int awfl_time_step_host(awfl_handle *h, double *const *host_fields, double crm_dt, int ncycles_override, int *ncycles_out);
 
+/* Number of member slabs awfl_time_step_host pipelines (copy of one slab overlaps the kernels of another; CRMs are
+ * independent, so results do not depend on it). Default 4 (or the environment variable AWFL_HOST_SLABS); 1 = copy
+ * everything, step, copy everything back. */
+int awfl_set_host_slabs(awfl_handle *h, int nslabs);
+
+/* awfl_time_step_host starts its slabs with a predicted sub-cycle count (the previous call's) before the CFL dt of the
+ * whole ensemble is known and redoes the step, un-overlapped, when the prediction was wrong: how often that happened. */
+long awfl_host_mispredictions(const awfl_handle *h);
+
 /* Dycore::compute_time_step (Dycore.h:65-102): min over cells of cfl*d/(|vel|+cs); result written to *dt_host. */
 int awfl_compute_time_step(awfl_handle *h, const awfl_fields *f, double cfl, double *dt_host);
 

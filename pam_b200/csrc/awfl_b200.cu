@@ -46,13 +46,19 @@ struct FctArgs {
 // blocks of a row cover its nx*nens (i, member) pairs; blockIdx.y = tracer. Every index is 32-bit and the row part is
 // block-uniform (the first version decoded a 64-bit linear cell index with three runtime divisions per thread and was
 // issue-bound at a third of the HBM rate: profiles/r01d, 2.7 ms per launch at NT=10).
-struct RowMap { int rblocks, rowlen; };
+struct RowMap { int rblocks, rowlen; };   // rowlen = nx * (members of the slab), rblocks = ceil(rowlen / blockDim.x)
+static RowMap row_map(const Geom &g, int threads) {
+  RowMap m;
+  m.rowlen = g.nx * g.ne; m.rblocks = (m.rowlen + threads - 1) / threads;
+  return m;
+}
+static unsigned row_blocks(const Geom &g, const RowMap &m) { return (unsigned)m.rblocks * (unsigned)(g.nz * g.ny); }
 __device__ __forceinline__ bool row_coords(const Geom &g, const RowMap m, long &cell, int &k, int &j, int &i, int &e) {
   const unsigned kj = blockIdx.x / (unsigned)m.rblocks, rb = blockIdx.x - kj * (unsigned)m.rblocks;
   const int r = (int)(rb * blockDim.x + threadIdx.x);
   k = (int)(kj / (unsigned)g.ny); j = (int)(kj - (unsigned)k * (unsigned)g.ny);
-  i = (int)((unsigned)r / (unsigned)g.nens); e = r - i * g.nens;
-  cell = (long)kj * m.rowlen + r;
+  i = (int)((unsigned)r / (unsigned)g.ne); e = g.e0 + (r - i * g.ne);
+  cell = ((long)kj * g.nx + i) * g.nens + e;
   return r < m.rowlen;
 }
 
@@ -162,10 +168,11 @@ __device__ __forceinline__ double atomic_min_pos(double *addr, double v) {
 
 __global__ void __launch_bounds__(256)
 k_coupler_to_dycore(const Geom g, const Phys ph, const FieldPtrs fp, int idWV, const unsigned char *adds_mass,
-                    const unsigned char *positive, double *q, double cfl, const double *dz, double *dt_min) {
-  const long cell = (long)blockIdx.x * blockDim.x + threadIdx.x;
+                    const unsigned char *positive, double *q, double cfl, const double *dz, double *dt_min, const RowMap rm) {
+  long cell; int k, j, i, e;
+  const bool in = row_coords(g, rm, cell, k, j, i, e);
   double dtc = INFINITY;
-  if (cell < g.ncell) {
+  if (in) {
     const long nc = g.ncell;
     const double rho_d = fp.f[0][cell], u = fp.f[1][cell], v = fp.f[2][cell], w = fp.f[3][cell], temp = fp.f[4][cell];
     const double rho_v = fp.tr[idWV][cell];
@@ -183,7 +190,6 @@ k_coupler_to_dycore(const Geom g, const Phys ph, const FieldPtrs fp, int idWV, c
     q[3 * nc + cell] = rho * w;
     q[4 * nc + cell] = rho * theta;
     if (dt_min) {
-      const int k = (int)(cell / ((long)g.ny * g.nx * g.nens)), e = (int)(cell % g.nens);
       const double rho2 = rho_d + rho_v;
       const double p = (rho_d * ph.R_d + rho_v * ph.R_v) * temp;
       const double c = sqrt(ph.gamma * p / rho2);
@@ -205,13 +211,13 @@ k_coupler_to_dycore(const Geom g, const Phys ph, const FieldPtrs fp, int idWV, c
 }
 
 __global__ void __launch_bounds__(256)
-k_cfl_only(const Geom g, const Phys ph, const FieldPtrs fp, int idWV, double cfl, const double *dz, double *dt_min) {
-  const long cell = (long)blockIdx.x * blockDim.x + threadIdx.x;
+k_cfl_only(const Geom g, const Phys ph, const FieldPtrs fp, int idWV, double cfl, const double *dz, double *dt_min, const RowMap rm) {
+  long cell; int k, j, i, e;
+  const bool in = row_coords(g, rm, cell, k, j, i, e);
   double dtc = INFINITY;
-  if (cell < g.ncell) {
+  if (in) {
     const double rho_d = fp.f[0][cell], u = fp.f[1][cell], v = fp.f[2][cell], w = fp.f[3][cell], temp = fp.f[4][cell];
     const double rho_v = fp.tr[idWV][cell];
-    const int k = (int)(cell / ((long)g.ny * g.nx * g.nens)), e = (int)(cell % g.nens);
     const double rho = rho_d + rho_v;
     const double p = (rho_d * ph.R_d + rho_v * ph.R_v) * temp;
     const double c = sqrt(ph.gamma * p / rho);
@@ -230,9 +236,10 @@ k_cfl_only(const Geom g, const Phys ph, const FieldPtrs fp, int idWV, double cfl
 }
 
 __global__ void __launch_bounds__(256)
-k_dycore_to_coupler(const Geom g, const Phys ph, const FieldPtrs fp, int idWV, const unsigned char *adds_mass, const double *q) {
-  const long cell = (long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (cell >= g.ncell) return;
+k_dycore_to_coupler(const Geom g, const Phys ph, const FieldPtrs fp, int idWV, const unsigned char *adds_mass, const double *q,
+                    const RowMap rm) {
+  long cell; int k, j, i, e;
+  if (!row_coords(g, rm, cell, k, j, i, e)) return;
   const long nc = g.ncell;
   const double rho = q[cell];
   const double u = q[nc + cell] / rho, v = q[2 * nc + cell] / rho, w = q[3 * nc + cell] / rho, theta = q[4 * nc + cell] / rho;
@@ -336,6 +343,11 @@ struct awfl_handle {
   std::vector<int> ev_class;     // class of event pair i (events 2i, 2i+1)
   size_t ev_used;
   double *stage_fields;  // staging buffer for the host-buffer entry point (5+nt fields)
+  int host_last_ncycles;      // sub-cycle count derived by the previous awfl_time_step_host (0 = none yet): the prediction
+  long host_mispredictions;   // calls whose prediction was wrong and were redone un-overlapped
+  int host_slabs;        // member slabs of the host-buffer entry point (copy/compute overlap); 1 = no pipelining
+  cudaStream_t s_in, s_out;              // copy streams of the host-buffer entry point
+  std::vector<cudaEvent_t> slab_ev;      // 2 events per slab: inputs on the device / results ready on the device
   double *tmp_state;     // scratch for awfl_compute_tendencies
 };
 
@@ -361,7 +373,8 @@ enum { KC_IN = 0, KC_OUT, KC_STATE_X, KC_STATE_Y, KC_STATE_Z, KC_TRACER_X, KC_TR
 struct ProfScope {
   awfl_handle *h;
   bool on;
-  ProfScope(awfl_handle *h_, int cls);
+  cudaStream_t st;
+  ProfScope(awfl_handle *h_, int cls, cudaStream_t st_ = nullptr);
   ~ProfScope();
 };
 
@@ -451,18 +464,18 @@ static void build_vertical(int ord, int nz, int nens, const double *dz, bool sha
     }
 }
 
-ProfScope::ProfScope(awfl_handle *h_, int cls) : h(h_), on(h_->prof) {
+ProfScope::ProfScope(awfl_handle *h_, int cls, cudaStream_t st_) : h(h_), on(h_->prof), st(st_ ? st_ : h_->stream) {
   h->launches++;
   if (!on) return;
   if (h->ev_used + 2 > h->ev_pool.size()) {
     for (int i = 0; i < 2; i++) { cudaEvent_t e; cudaEventCreate(&e); h->ev_pool.push_back(e); }
   }
   h->ev_class.push_back(cls);
-  cudaEventRecord(h->ev_pool[h->ev_used], h->stream);
+  cudaEventRecord(h->ev_pool[h->ev_used], st);
 }
 ProfScope::~ProfScope() {
   if (!on) return;
-  cudaEventRecord(h->ev_pool[h->ev_used + 1], h->stream);
+  cudaEventRecord(h->ev_pool[h->ev_used + 1], st);
   h->ev_used += 2;
 }
 
@@ -508,22 +521,21 @@ static int ensure_cvtab(awfl_handle *h) {
   return 0;
 }
 
-static void launch_state_sweep(awfl_handle *h, int dir, int mode, const SweepArgs &a) {
+static void launch_state_sweep(awfl_handle *h, const Geom &g, int dir, int mode, const SweepArgs &a) {
   ProfScope ps(h, KC_STATE_X + dir);
-  AWFL_ORD_DISPATCH(march_state(h->stream, h->g, h->ph, a, dir, mode, dir == 2 ? (h->use_cvtab ? 1 : 2) : 0));
+  AWFL_ORD_DISPATCH(march_state(h->stream, g, h->ph, a, dir, mode, dir == 2 ? (h->use_cvtab ? 1 : 2) : 0));
 }
 
-static void launch_tracer_sweep(awfl_handle *h, int dir, TracerSweepArgs a) {
-  if (h->g.nt == 0) return;
+static void launch_tracer_sweep(awfl_handle *h, const Geom &g, int dir, TracerSweepArgs a) {
+  if (g.nt == 0) return;
   ProfScope ps(h, KC_TRACER_X + dir);
-  AWFL_ORD_DISPATCH(march_tracer(h->stream, h->g, a, dir, dir == 2 ? (h->use_cvtab ? 1 : 2) : 0));
+  AWFL_ORD_DISPATCH(march_tracer(h->stream, g, a, dir, dir == 2 ? (h->use_cvtab ? 1 : 2) : 0));
 }
 
 // One semi-discrete right-hand side + stage combination.
 //   qin: stage input; q0: step-start state; qout: stage output.  mode 1: RK update, mode 2: tendencies to (st_out,tr_out)
-static void run_stage(awfl_handle *h, const double *qin, const double *q0, double *qout, double a, double b, double dt_stage,
+static void run_stage(awfl_handle *h, const Geom &g, const double *qin, const double *q0, double *qout, double a, double b, double dt_stage,
                       double dt_full, double sa, double sb, int mode, const double *fct_start, double *st_out, double *tr_out) {
-  const Geom &g = h->g;
   const int ndir = g.sim2d ? 2 : 3;
   const int dirs3[3] = {0, 1, 2}, dirs2[2] = {0, 2};
   const int *dirs = g.sim2d ? dirs2 : dirs3;
@@ -535,15 +547,14 @@ static void run_stage(awfl_handle *h, const double *qin, const double *q0, doubl
     s.qin = qin; s.qbase = q0; s.qout = mode == 2 ? st_out : qout; s.tend = h->tend; s.mflux = h->mflux[dir];
     s.dz = h->dz; s.grav_var = h->grav_var; s.vtab = h->vtab; s.rdz = h->rdz; s.vst = h->shared_grid ? 1 : g.nens;
     s.a = a; s.b = b; s.c = b * dt_full; s.first = d == 0; s.sbits = sbits_for(h, nn[dir]); s.labits = labits_for(h, dir);
-    launch_state_sweep(h, dir, last ? mode : 0, s);
+    launch_state_sweep(h, g, dir, last ? mode : 0, s);
     TracerSweepArgs t;
     t.qin = qin; t.mflux = h->mflux[dir]; t.tflux = h->tflux[dir]; t.vtab = h->vtab; t.vst = s.vst; t.sbits = s.sbits; t.labits = s.labits;
-    launch_tracer_sweep(h, dir, t);
+    launch_tracer_sweep(h, g, dir, t);
   }
   if (g.nt > 0) {
-    RowMap rm;
-    rm.rowlen = g.nx * g.nens; rm.rblocks = (rm.rowlen + 255) / 256;
-    const unsigned blocks = (unsigned)rm.rblocks * (unsigned)(g.nz * g.ny);
+    const RowMap rm = row_map(g, 256);
+    const unsigned blocks = row_blocks(g, rm);
     FctArgs f;
     f.q0 = q0; f.qs = qin; f.tfx = h->tflux[0]; f.tfy = h->tflux[1]; f.tfz = h->tflux[2]; f.fct_start = fct_start;
     f.mult = h->mult; f.dz = h->dz; f.rdz = h->rdz; f.rdx = 1.0 / g.dx; f.rdy = 1.0 / g.dy; f.positive = h->positive_d; f.sa = sa; f.sb = sb; f.dt = dt_stage;
@@ -592,6 +603,7 @@ int awfl_create(const awfl_config *cfg, awfl_handle **out) {
   g.nz = cfg->nz; g.ny = cfg->ny; g.nx = cfg->nx; g.nens = cfg->nens; g.nt = cfg->num_tracers;
   g.sim2d = cfg->ny == 1;
   g.ncell = (long)g.nz * g.ny * g.nx * g.nens;
+  g.e0 = 0; g.ne = g.nens;
   g.dx = cfg->xlen / g.nx; g.dy = cfg->ylen / g.ny;
   // Dycore.h:871-891
   const double R_d = cfg->R_d, cp_d = cfg->cp_d;
@@ -643,6 +655,12 @@ int awfl_create(const awfl_config *cfg, awfl_handle **out) {
   ALLOC(h->positive_d, nt); ALLOC(h->adds_mass_d, nt);
   ALLOC(h->trptr_d, sizeof(double *) * nt);
   h->stage_fields = nullptr; h->tmp_state = nullptr;
+  h->s_in = nullptr; h->s_out = nullptr; h->host_last_ncycles = 0; h->host_mispredictions = 0;
+  {
+    // member slabs of awfl_time_step_host: 4 by default (measured on C2); AWFL_HOST_SLABS overrides
+    const char *ev = getenv("AWFL_HOST_SLABS");
+    h->host_slabs = ev && atoi(ev) > 0 ? atoi(ev) : 4;
+  }
   if (cudaMallocHost((void **)&h->dt_min_h, sizeof(double)) != cudaSuccess) return bail("cudaMallocHost failed");
   cudaMemcpy(h->dz, cfg->dz_host, sizeof(double) * g.nz * g.nens, cudaMemcpyHostToDevice);
   {
@@ -670,6 +688,8 @@ void awfl_destroy(awfl_handle *h) {
   cudaFree(h->mult); cudaFree(h->dz); cudaFree(h->rdz); cudaFree(h->grav_var); cudaFree(h->vtab); cudaFree(h->vs2c); cudaFree(h->vwrl);
   cudaFree(h->pint); cudaFree(h->dt_min_d); cudaFree(h->mass_d); cudaFree(h->positive_d); cudaFree(h->adds_mass_d);
   cudaFree(h->trptr_d); cudaFree(h->stage_fields); cudaFree(h->tmp_state);
+  if (h->s_in) { cudaStreamDestroy(h->s_in); cudaStreamDestroy(h->s_out); }
+  for (cudaEvent_t e : h->slab_ev) cudaEventDestroy(e);
   if (h->dt_min_h) cudaFreeHost(h->dt_min_h);
   for (cudaEvent_t e : h->ev_pool) cudaEventDestroy(e);
   if (h->own_stream && h->stream) cudaStreamDestroy(h->stream);
@@ -732,8 +752,8 @@ int awfl_compute_time_step(awfl_handle *h, const awfl_fields *f, double cfl, dou
   if (make_field_ptrs(h, f, fp)) return 1;
   const double inf = INFINITY;
   CK(cudaMemcpyAsync(h->dt_min_d, &inf, sizeof(double), cudaMemcpyHostToDevice, h->stream));
-  const unsigned blocks = (unsigned)((h->g.ncell + 255) / 256);
-  k_cfl_only<<<blocks, 256, 0, h->stream>>>(h->g, h->ph, fp, h->cfg.idWV, cfl, h->dz, h->dt_min_d);
+  const RowMap rm = row_map(h->g, 256);
+  k_cfl_only<<<row_blocks(h->g, rm), 256, 0, h->stream>>>(h->g, h->ph, fp, h->cfg.idWV, cfl, h->dz, h->dt_min_d, rm);
   h->launches++;
   CK(cudaMemcpyAsync(h->dt_min_h, h->dt_min_d, sizeof(double), cudaMemcpyDeviceToHost, h->stream));
   CK(cudaStreamSynchronize(h->stream));
@@ -741,62 +761,174 @@ int awfl_compute_time_step(awfl_handle *h, const awfl_fields *f, double cfl, dou
   return 0;
 }
 
+// The three pieces of Dycore::timeStep (Dycore.h:107-255) on the member slab `g` describes (the whole ensemble, or one
+// slab of the host-buffer entry point); all work goes to h->stream.
+// (1) convert_coupler_to_dynamics + tracer clip + CFL minimum (Dycore.h:128-134,141)
+static void step_convert_in(awfl_handle *h, const Geom &g, const FieldPtrs &fp, bool need_dt, cudaStream_t st = nullptr) {
+  if (!st) st = h->stream;
+  ProfScope ps(h, KC_IN, st);
+  const RowMap rm = row_map(g, 256);
+  k_coupler_to_dycore<<<row_blocks(g, rm), 256, 0, st>>>(g, h->ph, fp, h->cfg.idWV, h->adds_mass_d, h->positive_d, h->Q[0], 0.8,
+                                                                h->dz, need_dt ? h->dt_min_d : nullptr, rm);
+}
+// (2) read the CFL minimum back and derive the sub-cycle count (Dycore.h:144): the only host synchronisation of a step
+static int step_ncycles(awfl_handle *h, double crm_dt, int *ncycles, cudaStream_t st = nullptr) {
+  if (!st) st = h->stream;
+  CK(cudaMemcpyAsync(h->dt_min_h, h->dt_min_d, sizeof(double), cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  const double dt_dyn = *h->dt_min_h;
+  if (!(dt_dyn > 0.0) || !isfinite(dt_dyn)) return fail(h, "awfl_time_step: non-finite CFL time step (NaN or non-positive state)");
+  *ncycles = (int)ceil(crm_dt / dt_dyn);
+  return 0;
+}
+// (3) ncycles SSPRK3 sub-cycles (Dycore.h:147-222; Q0 = step state, Q1/Q2 = stage states)
+static void step_advance(awfl_handle *h, const Geom &g, int ncycles, double dt) {
+  for (int c = 0; c < ncycles; c++) {
+    run_stage(h, g, h->Q[0], h->Q[0], h->Q[1], 0.0, 1.0, dt, dt, 1.0, 0.0, 1, nullptr, nullptr, nullptr);
+    run_stage(h, g, h->Q[1], h->Q[0], h->Q[2], 3.0 / 4.0, 1.0 / 4.0, (1.0 / 4.0) * dt, dt, 3.0 / 4.0, 1.0 / 4.0, 1, nullptr, nullptr, nullptr);
+    run_stage(h, g, h->Q[2], h->Q[0], h->Q[0], 1.0 / 3.0, 2.0 / 3.0, (2.0 / 3.0) * dt, dt, 1.0 / 3.0, 2.0 / 3.0, 1, nullptr, nullptr, nullptr);
+  }
+}
+// (4) convert_dynamics_to_coupler (Dycore.h:1281-1331)
+static void step_convert_out(awfl_handle *h, const Geom &g, const FieldPtrs &fp, cudaStream_t st = nullptr) {
+  if (!st) st = h->stream;
+  ProfScope ps(h, KC_OUT, st);
+  const RowMap rm = row_map(g, 256);
+  k_dycore_to_coupler<<<row_blocks(g, rm), 256, 0, st>>>(g, h->ph, fp, h->cfg.idWV, h->adds_mass_d, h->Q[0], rm);
+}
+
 int awfl_time_step(awfl_handle *h, const awfl_fields *f, double crm_dt, int ncycles_override, int *ncycles_out) {
   if (!(crm_dt > 0.0)) return fail(h, "awfl_time_step: crm_dt must be positive");
   FieldPtrs fp;
   if (make_field_ptrs(h, f, fp)) return 1;
   const Geom &g = h->g;
-  const unsigned blocks = (unsigned)((g.ncell + 255) / 256);
   const bool need_dt = ncycles_override <= 0;
   if (need_dt) {
     const double inf = INFINITY;
     CK(cudaMemcpyAsync(h->dt_min_d, &inf, sizeof(double), cudaMemcpyHostToDevice, h->stream));
   }
-  // Dycore.h:128-134,141
-  { ProfScope ps(h, KC_IN);
-    k_coupler_to_dycore<<<blocks, 256, 0, h->stream>>>(g, h->ph, fp, h->cfg.idWV, h->adds_mass_d, h->positive_d, h->Q[0], 0.8, h->dz,
-                                                       need_dt ? h->dt_min_d : nullptr); }
+  step_convert_in(h, g, fp, need_dt);
   int ncycles = ncycles_override;
-  if (need_dt) {
-    CK(cudaMemcpyAsync(h->dt_min_h, h->dt_min_d, sizeof(double), cudaMemcpyDeviceToHost, h->stream));
-    CK(cudaStreamSynchronize(h->stream));
-    const double dt_dyn = *h->dt_min_h;
-    if (!(dt_dyn > 0.0) || !isfinite(dt_dyn)) return fail(h, "awfl_time_step: non-finite CFL time step (NaN or non-positive state)");
-    ncycles = (int)ceil(crm_dt / dt_dyn);   // Dycore.h:144
-  }
+  if (need_dt && step_ncycles(h, crm_dt, &ncycles)) return 1;
   const double dt = crm_dt / ncycles;       // Dycore.h:145
   if (ensure_cvtab(h)) return 1;
-  for (int c = 0; c < ncycles; c++) {
-    // SSPRK3, Dycore.h:147-222. Q0 = step state, Q1/Q2 = stage states.
-    run_stage(h, h->Q[0], h->Q[0], h->Q[1], 0.0, 1.0, dt, dt, 1.0, 0.0, 1, nullptr, nullptr, nullptr);
-    run_stage(h, h->Q[1], h->Q[0], h->Q[2], 3.0 / 4.0, 1.0 / 4.0, (1.0 / 4.0) * dt, dt, 3.0 / 4.0, 1.0 / 4.0, 1, nullptr, nullptr, nullptr);
-    run_stage(h, h->Q[2], h->Q[0], h->Q[0], 1.0 / 3.0, 2.0 / 3.0, (2.0 / 3.0) * dt, dt, 1.0 / 3.0, 2.0 / 3.0, 1, nullptr, nullptr, nullptr);
-  }
-  { ProfScope ps(h, KC_OUT); k_dycore_to_coupler<<<blocks, 256, 0, h->stream>>>(g, h->ph, fp, h->cfg.idWV, h->adds_mass_d, h->Q[0]); }
+  step_advance(h, g, ncycles, dt);
+  step_convert_out(h, g, fp);
   CK(cudaGetLastError());
   if (ncycles_out) *ncycles_out = ncycles;
   return 0;
 }
 
+int awfl_set_host_slabs(awfl_handle *h, int nslabs) {
+  if (nslabs < 1) return fail(h, "awfl_set_host_slabs: need at least one slab");
+  h->host_slabs = nslabs;
+  return 0;
+}
+
+// Dycore::timeStep on HOST fields, pipelined over member slabs (multiples of 32 members; a slab is a strided column
+// block of every (cells, nens) field: cudaMemcpy2DAsync, row = the slab's members of one cell).
+//   copy-in stream : H2D of slab s, then its conversion kernel (+ CFL minimum)        s = 0..P-1, then the dt read-back
+//   compute stream : the SSPRK3 sub-cycles of slab s as soon as its conversion is done
+//   copy-out stream: dycore -> coupler conversion of slab s, then its D2H
+// The reference takes dt from the whole coupler (Dycore.h:141-145), so the sub-cycle count is only known when the LAST
+// slab has arrived. To overlap the copies with the kernels anyway the slabs start with a PREDICTED count -- the caller's
+// ncycles_override, else the count the previous call derived -- and nothing irreversible happens until the prediction is
+// checked against the CFL minimum over all members: the staged inputs stay untouched on the device (the out-conversion and
+// the D2H of every slab are only enqueued after the check), so a wrong prediction costs one plain, un-overlapped step
+// from those inputs and never changes a result. Without a prediction (first call) the slabs wait for the dt.
+// Results are identical to awfl_time_step on the same fields for any slab count (members never interact).
 int awfl_time_step_host(awfl_handle *h, double *const *host_fields, double crm_dt, int ncycles_override, int *ncycles_out) {
+  if (!(crm_dt > 0.0)) return fail(h, "awfl_time_step_host: crm_dt must be positive");
   const Geom &g = h->g;
   const int N = NS + g.nt;
   const size_t fb = sizeof(double) * (size_t)g.ncell;
   if (!h->stage_fields) CK(cudaMalloc((void **)&h->stage_fields, fb * N));
+  const int tiles = (g.nens + 31) / 32;
+  const int P = h->host_slabs < tiles ? h->host_slabs : tiles;
+  if (!h->s_in) {
+    CK(cudaStreamCreateWithFlags(&h->s_in, cudaStreamNonBlocking));
+    CK(cudaStreamCreateWithFlags(&h->s_out, cudaStreamNonBlocking));
+  }
+  while ((int)h->slab_ev.size() < 2 * P + 1) {
+    cudaEvent_t e;
+    CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    h->slab_ev.push_back(e);
+  }
   std::vector<double *> trp(g.nt);
-  for (int v = 0; v < N; v++) CK(cudaMemcpyAsync(h->stage_fields + (size_t)v * g.ncell, host_fields[v], fb, cudaMemcpyHostToDevice, h->stream));
   awfl_fields f;
   f.density_dry = h->stage_fields; f.uvel = h->stage_fields + g.ncell; f.vvel = h->stage_fields + 2 * g.ncell;
   f.wvel = h->stage_fields + 3 * g.ncell; f.temp = h->stage_fields + 4 * g.ncell;
   for (int t = 0; t < g.nt; t++) trp[t] = h->stage_fields + (size_t)(NS + t) * g.ncell;
   f.tracers = trp.data();
-  // the pointer table must outlive the async copy inside awfl_time_step: sync before trp goes out of scope
-  int rc = awfl_time_step(h, &f, crm_dt, ncycles_override, ncycles_out);
-  if (rc) return rc;
-  for (int v = 0; v < N; v++) CK(cudaMemcpyAsync(host_fields[v], h->stage_fields + (size_t)v * g.ncell, fb, cudaMemcpyDeviceToHost, h->stream));
+  FieldPtrs fp;
+  if (make_field_ptrs(h, &f, fp)) return 1;
+  const bool need_dt = ncycles_override <= 0;
+  if (need_dt) {
+    const double inf = INFINITY;
+    CK(cudaMemcpyAsync(h->dt_min_d, &inf, sizeof(double), cudaMemcpyHostToDevice, h->stream));
+  }
+  if (ensure_cvtab(h)) return 1;
+  // the copy-in stream must not run ahead of earlier work on the compute stream (staging buffer, tracer pointer table,
+  // dt reset)
+  CK(cudaEventRecord(h->slab_ev[2 * P], h->stream));
+  CK(cudaStreamWaitEvent(h->s_in, h->slab_ev[2 * P], 0));
+  const int predicted = need_dt ? h->host_last_ncycles : ncycles_override;
+  std::vector<Geom> slab(P, g);
+  const size_t rows = (size_t)g.nz * g.ny * g.nx, pitch = sizeof(double) * (size_t)g.nens;
+  for (int s = 0; s < P; s++) {
+    const int t0 = (int)((long)tiles * s / P), t1 = (int)((long)tiles * (s + 1) / P);
+    slab[s].e0 = 32 * t0;
+    slab[s].ne = (t1 == tiles ? g.nens : 32 * t1) - slab[s].e0;
+    for (int v = 0; v < N; v++) {
+      if (P == 1) CK(cudaMemcpyAsync(h->stage_fields + (size_t)v * g.ncell, host_fields[v], fb, cudaMemcpyHostToDevice, h->s_in));
+      else CK(cudaMemcpy2DAsync(h->stage_fields + (size_t)v * g.ncell + slab[s].e0, pitch, host_fields[v] + slab[s].e0, pitch,
+                                sizeof(double) * (size_t)slab[s].ne, rows, cudaMemcpyHostToDevice, h->s_in));
+    }
+    step_convert_in(h, slab[s], fp, need_dt, h->s_in);
+    CK(cudaEventRecord(h->slab_ev[2 * s], h->s_in));
+    if (predicted > 0) {
+      CK(cudaStreamWaitEvent(h->stream, h->slab_ev[2 * s], 0));
+      step_advance(h, slab[s], predicted, crm_dt / predicted);
+      CK(cudaEventRecord(h->slab_ev[2 * s + 1], h->stream));
+    }
+  }
+  int ncycles = ncycles_override;
+  if (need_dt && step_ncycles(h, crm_dt, &ncycles, h->s_in)) return 1;
+  h->host_last_ncycles = ncycles;
+  const double dt = crm_dt / ncycles;       // Dycore.h:145
+  if (predicted > 0 && predicted != ncycles) {
+    // misprediction: redo the whole step from the staged inputs (still intact), un-overlapped
+    h->host_mispredictions++;
+    step_convert_in(h, g, fp, false);
+    step_advance(h, g, ncycles, dt);
+    step_convert_out(h, g, fp);
+    CK(cudaEventRecord(h->slab_ev[1], h->stream));
+    CK(cudaStreamWaitEvent(h->s_out, h->slab_ev[1], 0));
+    for (int v = 0; v < N; v++) CK(cudaMemcpyAsync(host_fields[v], h->stage_fields + (size_t)v * g.ncell, fb, cudaMemcpyDeviceToHost, h->s_out));
+  } else {
+    for (int s = 0; s < P; s++) {
+      if (predicted <= 0) {
+        if (s == 0) CK(cudaStreamWaitEvent(h->stream, h->slab_ev[2 * (P - 1)], 0));
+        step_advance(h, slab[s], ncycles, dt);
+        CK(cudaEventRecord(h->slab_ev[2 * s + 1], h->stream));
+      }
+      CK(cudaStreamWaitEvent(h->s_out, h->slab_ev[2 * s + 1], 0));
+      step_convert_out(h, slab[s], fp, h->s_out);
+      for (int v = 0; v < N; v++) {
+        if (P == 1) CK(cudaMemcpyAsync(host_fields[v], h->stage_fields + (size_t)v * g.ncell, fb, cudaMemcpyDeviceToHost, h->s_out));
+        else CK(cudaMemcpy2DAsync(host_fields[v] + slab[s].e0, pitch, h->stage_fields + (size_t)v * g.ncell + slab[s].e0, pitch,
+                                  sizeof(double) * (size_t)slab[s].ne, rows, cudaMemcpyDeviceToHost, h->s_out));
+      }
+    }
+  }
+  CK(cudaGetLastError());
+  CK(cudaStreamSynchronize(h->s_out));
   CK(cudaStreamSynchronize(h->stream));
+  if (ncycles_out) *ncycles_out = ncycles;
   return 0;
 }
+
+long awfl_host_mispredictions(const awfl_handle *h) { return h->host_mispredictions; }
 
 int awfl_compute_tendencies(awfl_handle *h, const double *state, const double *tracers, const double *fct_start, double dt,
                             double *state_tend, double *tracers_tend) {
@@ -806,7 +938,7 @@ int awfl_compute_tendencies(awfl_handle *h, const double *state, const double *t
   CK(cudaMemcpyAsync(h->Q[1], state, fb * NS, cudaMemcpyDeviceToDevice, h->stream));
   if (g.nt > 0) CK(cudaMemcpyAsync(h->Q[1] + (size_t)NS * g.ncell, tracers, fb * g.nt, cudaMemcpyDeviceToDevice, h->stream));
   if (ensure_cvtab(h)) return 1;
-  run_stage(h, h->Q[1], h->Q[1], nullptr, 0.0, 1.0, dt, dt, 1.0, 0.0, 2, fct_start, state_tend, tracers_tend);
+  run_stage(h, h->g, h->Q[1], h->Q[1], nullptr, 0.0, 1.0, dt, dt, 1.0, 0.0, 2, fct_start, state_tend, tracers_tend);
   CK(cudaGetLastError());
   CK(cudaStreamSynchronize(h->stream));
   return 0;
@@ -823,8 +955,8 @@ int awfl_declare_hydrostatic(awfl_handle *h, const awfl_fields *f, const awfl_gc
   } else {
     FieldPtrs fp;
     if (make_field_ptrs(h, f, fp)) return 1;
-    const unsigned blocks = (unsigned)((g.ncell + 255) / 256);
-    k_coupler_to_dycore<<<blocks, 256, 0, h->stream>>>(g, h->ph, fp, h->cfg.idWV, h->adds_mass_d, h->positive_d, h->Q[1], 0.8, h->dz, nullptr);
+    const RowMap rm = row_map(g, 256);
+    k_coupler_to_dycore<<<row_blocks(g, rm), 256, 0, h->stream>>>(g, h->ph, fp, h->cfg.idWV, h->adds_mass_d, h->positive_d, h->Q[1], 0.8, h->dz, nullptr, rm);
     h->launches++;
     a.q = h->Q[1];
   }
@@ -842,8 +974,8 @@ int awfl_compute_mass(awfl_handle *h, const awfl_fields *f, double *out_host) {
   const Geom &g = h->g;
   FieldPtrs fp;
   if (make_field_ptrs(h, f, fp)) return 1;
-  const unsigned blocks = (unsigned)((g.ncell + 255) / 256);
-  k_coupler_to_dycore<<<blocks, 256, 0, h->stream>>>(g, h->ph, fp, h->cfg.idWV, h->adds_mass_d, h->positive_d, h->Q[1], 0.8, h->dz, nullptr);
+  const RowMap rm = row_map(g, 256);
+  k_coupler_to_dycore<<<row_blocks(g, rm), 256, 0, h->stream>>>(g, h->ph, fp, h->cfg.idWV, h->adds_mass_d, h->positive_d, h->Q[1], 0.8, h->dz, nullptr, rm);
   h->launches++;
   const long n = (long)(g.nt + 2) * g.nens;
   k_mass<<<(unsigned)((n + 127) / 128), 128, 0, h->stream>>>(g, h->Q[1], h->dz, h->mass_d);

@@ -27,7 +27,7 @@ static void launch_march(void (*kernel)(KArgs...), dim3 blocks, size_t bytes, cu
 // lines_per_warp > 1 (tracer march): adjacent levels for the horizontal marches (first line index, inside blockIdx.z),
 // adjacent columns for the vertical march (second line index = blockIdx.y)
 static dim3 march_grid(const Geom &g, int dir, int sbits, int labits, int ntr, int lines_per_warp) {
-  const unsigned netile = (unsigned)(g.nens + 31) / 32;
+  const unsigned netile = (unsigned)(g.ne + 31) / 32;   // member tiles of the slab
   unsigned lb = dir == 0 ? g.ny : g.nx;
   if (dir == 2) lb = (lb + lines_per_warp - 1) / lines_per_warp;
   return dim3(netile, lb, (unsigned)ntr << (labits + sbits));

@@ -12,6 +12,10 @@ struct Geom {
   int sim2d;
   long ncell;     // nz*ny*nx*nens
   double dx, dy;
+  // Member slab a launch works on: members [e0, e0+ne) of the nens stored ones (e0 a multiple of 32). The whole ensemble
+  // is (0, nens); awfl_time_step_host runs the step slab by slab so that host<->device copies of one slab overlap the
+  // kernels of another (CRMs are independent: no kernel reads across members).
+  int e0, ne;
 };
 struct Phys {
   double R_d, R_v, C0, gamma, grav;

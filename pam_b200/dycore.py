@@ -209,6 +209,14 @@ class Dycore:
         self._rc(self.lib.awfl_time_step_host(self.h, arr, float(crm_dt), int(ncycles), C.byref(n)), "awfl_time_step_host")
         return n.value
 
+    def set_host_slabs(self, nslabs):
+        """Member slabs pipelined by time_step_host (copies of one slab overlap the kernels of another)."""
+        self._rc(self.lib.awfl_set_host_slabs(self.h, int(nslabs)), "awfl_set_host_slabs")
+
+    def host_mispredictions(self):
+        """Calls of time_step_host whose predicted sub-cycle count was wrong (redone un-overlapped)."""
+        return self.lib.awfl_host_mispredictions(self.h)
+
     def profile_begin(self):
         self._rc(self.lib.awfl_profile_begin(self.h), "awfl_profile_begin")
 

@@ -191,6 +191,46 @@ def test_fixed_ncycles_and_host_buffer_entry_point_agree():
         assert np.array_equal(a, got[n]), n      # same kernels, same inputs: bit-identical
 
 
+@pytest.mark.parametrize("nens,slabs,ny", [(100, 1, 1), (100, 3, 1), (100, 4, 1), (40, 8, 1), (70, 2, 3)])
+def test_host_buffer_member_slabs_are_bit_identical(nens, slabs, ny):
+    """awfl_time_step_host pipelines member slabs (copy/compute overlap); CRMs are independent and the CFL dt is taken
+    over all members before any slab advances, so every slab count must give the bits of the device-resident step --
+    including a ragged last slab (nens not a multiple of 32) and more slabs than 32-member tiles."""
+    case = syn.make_case(12, ny, 10 if ny == 1 else 6, nens, tracers=syn.TRACERS_NT1, grid="tanh")
+    c, d = H.make_gpu(case, 5, crm_dt=2.0)
+    d.declare_current_profile_as_hydrostatic(c)
+    names = list(H.STATE_FIELDS) + c.get_tracer_names()
+    host = [np.ascontiguousarray(case["fields"][n]).copy() for n in names]
+    d.set_host_slabs(slabs)
+    n1 = d.timeStep(c)
+    n2 = d.time_step_host(host, 2.0)             # CFL dt computed over all slabs
+    assert n1 == n2
+    got = H.gpu_fields(c)
+    for n, a in zip(names, host):
+        assert np.array_equal(a, got[n]), n
+    # second step: the slabs now start with the predicted sub-cycle count (the first call's) before the dt is known
+    n3 = d.timeStep(c)
+    n4 = d.time_step_host(host, 2.0)
+    assert n3 == n4 and d.host_mispredictions() == 0
+    got = H.gpu_fields(c)
+    for n, a in zip(names, host):
+        assert np.array_equal(a, got[n]), n
+    # third step with another crm_dt: the prediction is wrong, the step is redone from the staged inputs
+    c.set_option("crm_dt", 5.0)
+    n5 = d.timeStep(c)
+    n6 = d.time_step_host(host, 5.0)
+    assert n5 == n6 and n5 != n3 and d.host_mispredictions() == 1
+    got = H.gpu_fields(c)
+    for n, a in zip(names, host):
+        assert np.array_equal(a, got[n]), n
+    # fixed sub-cycle count: no dt, no prediction to check
+    assert d.timeStep(c, ncycles=3) == 3
+    assert d.time_step_host(host, 5.0, ncycles=3) == 3
+    got = H.gpu_fields(c)
+    for n, a in zip(names, host):
+        assert np.array_equal(a, got[n]), n
+
+
 def test_errors_are_reported_not_swallowed():
     from pam_b200 import PamCoupler, Dycore
     c = PamCoupler("cuda:0")

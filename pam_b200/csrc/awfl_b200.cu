@@ -416,8 +416,21 @@ static void ideal_weights(int ord, double *idl) {
   for (int i = 0; i < m + 1; i++) idl[i] = raw[i] / (sum + 1.0e-20);
 }
 
+// Coefficient-space maps of the "row" form (tools/gen_tables.py tv_rows): glo (hs x hs), ghi (ord x ord), row-major.
+static void tv_row_maps(int ord, std::vector<double> &glo, std::vector<double> &ghi) {
+  static const double g3l[2][2] = AWFL_GLO_3_INIT, g3h[3][3] = AWFL_GHI_3_INIT;
+  static const double g5l[3][3] = AWFL_GLO_5_INIT, g5h[5][5] = AWFL_GHI_5_INIT;
+  static const double g7l[4][4] = AWFL_GLO_7_INIT, g7h[7][7] = AWFL_GHI_7_INIT;
+  static const double g9l[5][5] = AWFL_GLO_9_INIT, g9h[9][9] = AWFL_GHI_9_INIT;
+  const int hs = (ord + 1) / 2;
+  const double *l = ord == 3 ? &g3l[0][0] : ord == 5 ? &g5l[0][0] : ord == 7 ? &g7l[0][0] : &g9l[0][0];
+  const double *hh = ord == 3 ? &g3h[0][0] : ord == 5 ? &g5h[0][0] : ord == 7 ? &g7h[0][0] : &g9h[0][0];
+  glo.assign(l, l + hs * hs);
+  ghi.assign(hh, hh + ord * ord);
+}
+
 // Builds vs2c (nz+2,ord,ord,nens), vwrl (nz+2,hs,hs,hs,nens) exactly as the reference does, and the kernel table
-// vtab: per level [lo(hs^3) | bridge(ord^2)], element-major, ensemble fastest (or no ensemble axis if shared).
+// vtab: per level [rlo(hs^3) | rhi(ord^2)] in row form, element-major, ensemble fastest (or no ensemble axis if shared).
 static void build_vertical(int ord, int nz, int nens, const double *dz, bool shared, std::vector<double> &vs2c,
                            std::vector<double> &vwrl, std::vector<double> &vtab) {
   const int hs = (ord + 1) / 2, nel = hs * hs * hs + ord * ord;
@@ -426,6 +439,8 @@ static void build_vertical(int ord, int nz, int nens, const double *dz, bool sha
   vtab.assign((size_t)(nz + 2) * nel * (shared ? 1 : nens), 0.0);
   std::vector<double> idl(hs + 1);
   ideal_weights(ord, idl.data());
+  std::vector<double> glo, ghi;
+  tv_row_maps(ord, glo, ghi);
   std::vector<double> dzl(ord), locs(ord + 1), hi(ord * ord), lo(hs * hs), ll(hs + 1), los(hs * hs * hs);
   for (int k = 0; k < nz + 2; k++)
     for (int e = 0; e < nens; e++) {
@@ -459,8 +474,20 @@ static void build_vertical(int ord, int nz, int nens, const double *dz, bool sha
           for (int ii = 0; ii < hs; ii++) br[(i + s) * ord + ii] -= idl[i] * los[(i * hs + s) * hs + ii];
       for (int q = 0; q < ord * ord; q++) br[q] /= idl[hs];
       const size_t st = shared ? 1 : nens, off = shared ? 0 : e;
-      for (int q = 0; q < hs * hs * hs; q++) vtab[((size_t)k * nel + q) * st + off] = los[q];
-      for (int q = 0; q < ord * ord; q++) vtab[((size_t)k * nel + hs * hs * hs + q) * st + off] = br[q];
+      // kernel table in "row" form (awfl_weno.cuh): rlo[i][r][s] = sum_ii glo[r][ii]*lo_i[s][ii], rhi[r][s] = sum_ii ghi[r][ii]*br[s][ii]
+      for (int i = 0; i < hs; i++)
+        for (int r = 0; r < hs; r++)
+          for (int s2 = 0; s2 < hs; s2++) {
+            double acc = 0.0;
+            for (int ii = 0; ii < hs; ii++) acc += glo[r * hs + ii] * los[(i * hs + s2) * hs + ii];
+            vtab[((size_t)k * nel + (i * hs + r) * hs + s2) * st + off] = acc;
+          }
+      for (int r = 0; r < ord; r++)
+        for (int s2 = 0; s2 < ord; s2++) {
+          double acc = 0.0;
+          for (int ii = 0; ii < ord; ii++) acc += ghi[r * ord + ii] * br[s2 * ord + ii];
+          vtab[((size_t)k * nel + hs * hs * hs + r * ord + s2) * st + off] = acc;
+        }
     }
 }
 

@@ -125,8 +125,18 @@ template <int ORD> struct MatSel<ORD, 2> {
 //   MODE 1: last sweep: finish the tendency and write qout = a*qbase + b*roundtrip(qin) + c*tend
 //   MODE 2: last sweep: finish the tendency and write it to qout (tendency-level parity entry point)
 // ---------------------------------------------------------------------------------------------------------------
+// Register budget of the state march (one-warp blocks: 65536 / (32 * regs) resident warps per SM). Measured on B200
+// (profiles/r01g): ord 5 x/y march 168 (12 warps), z march 144 (14 warps; at 128 ptxas spills the loop control, and
+// the reloads stall every R2UR of the uniform march position on the load scoreboard), ord 3 128, ord 7/9 255.
+#ifndef AWFL_MAXNREG_Z
+#define AWFL_MAXNREG_Z 144
+#endif
+#ifndef AWFL_MAXNREG_H
+#define AWFL_MAXNREG_H 168
+#endif
+#define AWFL_STATE_BOUNDS __launch_bounds__(MT) __maxnreg__(ORD == 3 ? 128 : (ORD == 5 ? (DIR == 2 ? AWFL_MAXNREG_Z : AWFL_MAXNREG_H) : 255))
 template <int ORD, int DIR, int MODE, int VT>
-__global__ void __launch_bounds__(MT, DIR == 2 ? MarchCfg<ORD>::MINB_Z : MarchCfg<ORD>::MINB)
+__global__ void AWFL_STATE_BOUNDS
 k_march_state(const Geom g, const Phys ph, const SweepArgs a) {
   constexpr int HS = (ORD + 1) / 2;
   constexpr double cs = 350.0;             // Dycore.h:335

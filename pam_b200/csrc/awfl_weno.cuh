@@ -5,6 +5,10 @@
 //   * the "bridge" polynomial (WenoLimiter.h:131-138) is one mat-vec with a precomputed matrix
 //     B = (sten_to_coefs - sum_i idl_i*embed(weno_lower_i)) / idl_m   (tools/gen_tables.py; per level on the host
 //     for the vertical matrices), which removes ord divides and hs*hs FMAs per reconstruction;
+//   * no candidate polynomial is formed coefficient by coefficient: its stencil is mapped straight to the even part of
+//     its edge values and to the factors p_k of its total variation (TV = sum p_k^2, L D L^T of coefs_to_tv; the odd
+//     part of the edge values is p_1/2) -- 131 FP64 instructions per ord-5 reconstruction on a uniform grid instead of
+//     156 (the bridge rows are even / odd in the stencil there), 144 with per-level vertical matrices;
 //   * every division by a strictly positive quantity is a MUFU.RCP64H seed + two Newton steps (no slow path);
 //   * the second convexify (WenoLimiter.h:166) is applied once to the blended edge values instead of to each weight;
 //   * the blended polynomial is evaluated at BOTH cell edges from its even/odd parts, so one set of WENO weights per
@@ -27,58 +31,49 @@ template <int N> constexpr MapTab<N> make_map(const double (&d)[N]) {
   return t;
 }
 
-// Every table exists twice: a constexpr copy (compile-time structure: which entries are zero) and a __constant__ copy
-// whose entries the FP64 instructions read straight from the constant bank as c[bank][offset] operands. (Folded into
-// the instruction stream as immediates, each 64-bit constant costs two extra MOVs per use: profiles/r01b measured as
-// many non-FP64 as FP64 instructions in the x march.)
+// Every table exists twice: a constexpr copy (compile-time structure: which entries are zero, which rows are even / odd)
+// and a __constant__ copy whose entries the FP64 instructions read straight from the constant bank as c[bank][offset]
+// operands. (Folded into the instruction stream as immediates, each 64-bit constant costs two extra MOVs per use:
+// profiles/r01b measured as many non-FP64 as FP64 instructions in the x march.)
+//
+// "Row" form of a candidate polynomial (tools/gen_tables.py, tv_rows): ONE matrix applied to the stencil gives
+//   row 0      e   = even part of the edge values            p(-1/2) = e - o,  p(+1/2) = e + o
+//   rows 1..   p_k = the factors of the truncated total variation, TV = sum_k p_k^2   (L D L^T of coefs_to_tv)
+// and the odd part is o = p_1 / 2 for every order, so the polynomial coefficients themselves are never formed:
+// rlo[i][r][s] for the (ord+1)/2 low-order stencils, rhi[r][s] for the bridge polynomial (WenoLimiter.h:131-138 folded
+// into the matrix). ghi/glo are the same maps in coefficient space, applied on the host to the per-level vertical
+// matrices.
 #define AWFL_DEFINE_CST(O)                                                                                      \
   namespace ctab##O {                                                                                           \
     constexpr int HS = (O + 1) / 2;                                                                             \
     constexpr double idl_h[HS + 1] = AWFL_IDL_##O##_INIT;                                                       \
-    static __constant__ double lo[HS][HS][HS] = AWFL_WRL_##O##_INIT;                                            \
-    static __constant__ double br[O][O] = AWFL_BRIDGE_##O##_INIT;                                               \
+    static __constant__ double rlo[HS][HS][HS] = AWFL_RLO_##O##_INIT;                                           \
+    static __constant__ double rhi[O][O] = AWFL_RHI_##O##_INIT;                                                 \
     static __constant__ double idl[HS + 1] = AWFL_IDL_##O##_INIT;                                               \
     static __constant__ MapTab<HS + 1> map = make_map<HS + 1>(idl_h);                                           \
-    static __constant__ double tvlo[AWFL_TVLO_N_##O] = AWFL_TVLO_C_##O##_INIT;                                  \
-    static __constant__ double tvhi[AWFL_TVHI_N_##O] = AWFL_TVHI_C_##O##_INIT;                                  \
     static __constant__ double misc[3] = {AWFL_SIGMA_##O, 1.0 / HS, 1.0e-20};                                   \
   }                                                                                                             \
   template <> struct Cst<O> {                                                                                   \
     static constexpr int HS = (O + 1) / 2;                                                                      \
-    static __device__ __forceinline__ bool lo_nz(int i, int s, int ii) {                                        \
-      constexpr double T[HS][HS][HS] = AWFL_WRL_##O##_INIT;                                                     \
-      return T[i][s][ii] != 0.0;                                                                                \
+    static __device__ __forceinline__ bool lo_nz(int i, int r, int s) {                                         \
+      constexpr double T[HS][HS][HS] = AWFL_RLO_##O##_INIT;                                                     \
+      return T[i][r][s] != 0.0;                                                                                 \
     }                                                                                                           \
-    static __device__ __forceinline__ bool br_nz(int s, int ii) {                                               \
-      constexpr double T[O][O] = AWFL_BRIDGE_##O##_INIT;                                                        \
-      return T[s][ii] != 0.0;                                                                                   \
+    static __device__ __forceinline__ bool hi_nz(int r, int s) {                                                \
+      constexpr double T[O][O] = AWFL_RHI_##O##_INIT;                                                           \
+      return T[r][s] != 0.0;                                                                                    \
     }                                                                                                           \
-    static __device__ __forceinline__ double lo(int i, int s, int ii) { return ctab##O::lo[i][s][ii]; }         \
-    static __device__ __forceinline__ double br(int s, int ii) { return ctab##O::br[s][ii]; }                   \
+    static __device__ __forceinline__ bool hi_even(int r) {                                                     \
+      constexpr int T[O] = AWFL_RHI_PAR_##O##_INIT;                                                             \
+      return T[r] > 0;                                                                                          \
+    }                                                                                                           \
+    static __device__ __forceinline__ double lo(int i, int r, int s) { return ctab##O::rlo[i][r][s]; }          \
+    static __device__ __forceinline__ double hi(int r, int s) { return ctab##O::rhi[r][s]; }                    \
     static __device__ __forceinline__ double idl(int i) { return ctab##O::idl[i]; }                             \
     static __device__ __forceinline__ double map(int i, int k) { return ctab##O::map.v[i][k]; }                 \
     static __device__ __forceinline__ double sigma() { return ctab##O::misc[0]; }                               \
     static __device__ __forceinline__ double rhs() { return ctab##O::misc[1]; }                                 \
     static __device__ __forceinline__ double eps() { return ctab##O::misc[2]; }                                 \
-    /* TransformMatrices.h coefs_to_tv for hs and ord coefficients (truncated squared-derivative integrals) */  \
-    static __device__ __forceinline__ double tv_lo(const double (&a)[HS]) {                                     \
-      constexpr int N = AWFL_TVLO_N_##O;                                                                        \
-      constexpr int I[N] = AWFL_TVLO_I_##O##_INIT;                                                              \
-      constexpr int J[N] = AWFL_TVLO_J_##O##_INIT;                                                              \
-      constexpr double C[N] = AWFL_TVLO_C_##O##_INIT;                                                           \
-      double r = C[0] == 1.0 ? a[I[0]] * a[J[0]] : (ctab##O::tvlo[0] * a[I[0]]) * a[J[0]];                      \
-      _Pragma("unroll") for (int t = 1; t < N; t++) r = fma(ctab##O::tvlo[t] * a[I[t]], a[J[t]], r);            \
-      return r;                                                                                                 \
-    }                                                                                                           \
-    static __device__ __forceinline__ double tv_hi(const double (&a)[O]) {                                      \
-      constexpr int N = AWFL_TVHI_N_##O;                                                                        \
-      constexpr int I[N] = AWFL_TVHI_I_##O##_INIT;                                                              \
-      constexpr int J[N] = AWFL_TVHI_J_##O##_INIT;                                                              \
-      constexpr double C[N] = AWFL_TVHI_C_##O##_INIT;                                                           \
-      double r = C[0] == 1.0 ? a[I[0]] * a[J[0]] : (ctab##O::tvhi[0] * a[I[0]]) * a[J[0]];                      \
-      _Pragma("unroll") for (int t = 1; t < N; t++) r = fma(ctab##O::tvhi[t] * a[I[t]], a[J[t]], r);            \
-      return r;                                                                                                 \
-    }                                                                                                           \
   };
 
 // one translation unit per order: only that order's tables take constant-bank space
@@ -109,25 +104,25 @@ __device__ __forceinline__ double rcp_pos(double x) {
   return fma(r, t, r);
 }
 
-// Horizontal (uniform dx) matrices: compile-time constants folded into FMA immediates / constant bank.
+// Horizontal (uniform dx) matrices: constant-bank tables with compile-time structure (zeros, even / odd bridge rows).
 template <int ORD> struct HMat {
   static constexpr bool is_const = true;
-  __device__ __forceinline__ double lo(int i, int s, int ii) const { return Cst<ORD>::lo(i, s, ii); }
-  __device__ __forceinline__ double br(int s, int ii) const { return Cst<ORD>::br(s, ii); }
-  __device__ __forceinline__ bool lo_nz(int i, int s, int ii) const { return Cst<ORD>::lo_nz(i, s, ii); }
-  __device__ __forceinline__ bool br_nz(int s, int ii) const { return Cst<ORD>::br_nz(s, ii); }
+  __device__ __forceinline__ double lo(int i, int r, int s) const { return Cst<ORD>::lo(i, r, s); }
+  __device__ __forceinline__ double hi(int r, int s) const { return Cst<ORD>::hi(r, s); }
+  __device__ __forceinline__ bool lo_nz(int i, int r, int s) const { return Cst<ORD>::lo_nz(i, r, s); }
+  __device__ __forceinline__ bool hi_nz(int r, int s) const { return Cst<ORD>::hi_nz(r, s); }
 };
 
 // Vertical (variable dz) matrices: runtime table of one level, element stride `st`
-// (1 when all ensemble members share one vertical grid, nens otherwise). Layout per level: lo[HS][HS][HS], br[ORD][ORD].
+// (1 when all ensemble members share one vertical grid, nens otherwise). Layout per level: rlo[HS][HS][HS], rhi[ORD][ORD].
 template <int ORD> struct VMat {
   static constexpr bool is_const = false;
   static constexpr int HS = (ORD + 1) / 2;
   static constexpr int NEL = HS * HS * HS + ORD * ORD;
   const double *p;
   long st;
-  __device__ __forceinline__ double lo(int i, int s, int ii) const { return __ldg(p + ((i * HS + s) * HS + ii) * st); }
-  __device__ __forceinline__ double br(int s, int ii) const { return __ldg(p + (HS * HS * HS + s * ORD + ii) * st); }
+  __device__ __forceinline__ double lo(int i, int r, int s) const { return __ldg(p + ((i * HS + r) * HS + s) * st); }
+  __device__ __forceinline__ double hi(int r, int s) const { return __ldg(p + (HS * HS * HS + r * ORD + s) * st); }
 };
 
 // Vertical matrices of a grid shared by all ensemble members, held in the constant bank: the level index is uniform
@@ -142,8 +137,8 @@ template <int ORD> struct CMat {
   static constexpr int HS = (ORD + 1) / 2;
   static constexpr int NEL = HS * HS * HS + ORD * ORD;
   int base;
-  __device__ __forceinline__ double lo(int i, int s, int ii) const { return c_vtab[base + (i * HS + s) * HS + ii]; }
-  __device__ __forceinline__ double br(int s, int ii) const { return c_vtab[base + HS * HS * HS + s * ORD + ii]; }
+  __device__ __forceinline__ double lo(int i, int r, int s) const { return c_vtab[base + (i * HS + r) * HS + s]; }
+  __device__ __forceinline__ double hi(int r, int s) const { return c_vtab[base + HS * HS * HS + r * ORD + s]; }
 };
 
 // pr[i] = product of all t[j], j != i (prefix/suffix products, 3N-5 multiplications for N >= 3)
@@ -161,11 +156,25 @@ template <int N> __device__ __forceinline__ void others_product(const double (&t
   for (int i = 1; i < N - 1; i++) pr[i] = pre[i - 1] * suf[i + 1];
 }
 
-template <class M> __device__ __forceinline__ bool nonzero_lo(const M &m, int i, int s, int ii) {
-  if constexpr (M::is_const) return m.lo_nz(i, s, ii); else return true;
+// sum of N values as a balanced tree (dependency depth log2 N instead of N: the weight computation is the
+// latency-critical part of a reconstruction)
+template <int N> __device__ __forceinline__ double tree_sum(const double (&x)[N]) {
+  double y[N];
+#pragma unroll
+  for (int i = 0; i < N; i++) y[i] = x[i];
+#pragma unroll
+  for (int w = 1; w < N; w *= 2) {
+#pragma unroll
+    for (int i = 0; i + w < N; i += 2 * w) y[i] += y[i + w];
+  }
+  return y[0];
 }
-template <class M> __device__ __forceinline__ bool nonzero_br(const M &m, int s, int ii) {
-  if constexpr (M::is_const) return m.br_nz(s, ii); else return true;
+
+template <class M> __device__ __forceinline__ bool nonzero_lo(const M &m, int i, int r, int s) {
+  if constexpr (M::is_const) return m.lo_nz(i, r, s); else return true;
+}
+template <class M> __device__ __forceinline__ bool nonzero_hi(const M &m, int r, int s) {
+  if constexpr (M::is_const) return m.hi_nz(r, s); else return true;
 }
 
 // WENO-limited polynomials of the centre cell of NV stencils u[v][0..ORD-1] at once, each returned as its even (E) and odd
@@ -177,52 +186,80 @@ __device__ __forceinline__ void weno_EO_n(const double (&u)[NV][ORD], const M &m
   constexpr int HS = (ORD + 1) / 2;
   constexpr int N = HS + 1;
   using C = Cst<ORD>;
-  double alo[NV][HS][HS], ab[NV][ORD];
+  // per candidate polynomial: even edge part e, twice the odd edge part o2 (= p_1), total variation tv
+  double e[NV][N], o2[NV][N], tv[NV][N];
 #pragma unroll
   for (int i = 0; i < HS; i++) {
 #pragma unroll
-    for (int ii = 0; ii < HS; ii++) {
+    for (int r = 0; r < HS; r++) {
       double t[NV];
+      bool started = false;
 #pragma unroll
-      for (int v = 0; v < NV; v++) t[v] = m.lo(i, 0, ii) * u[v][i];
+      for (int s = 0; s < HS; s++) {
+        if (!nonzero_lo(m, i, r, s)) continue;
 #pragma unroll
-      for (int s = 1; s < HS; s++) {
-        if (nonzero_lo(m, i, s, ii)) {
-#pragma unroll
-          for (int v = 0; v < NV; v++) t[v] = fma(m.lo(i, s, ii), u[v][i + s], t[v]);
-        }
+        for (int v = 0; v < NV; v++) t[v] = started ? fma(m.lo(i, r, s), u[v][i + s], t[v]) : m.lo(i, r, s) * u[v][i + s];
+        started = true;
       }
 #pragma unroll
-      for (int v = 0; v < NV; v++) alo[v][i][ii] = t[v];
+      for (int v = 0; v < NV; v++) {
+        if (r == 0) e[v][i] = t[v];
+        else if (r == 1) { o2[v][i] = t[v]; tv[v][i] = t[v] * t[v]; }
+        else tv[v][i] = fma(t[v], t[v], tv[v][i]);
+      }
+    }
+  }
+  // bridge polynomial. On a uniform grid its rows are even or odd in the stencil (RHI_PAR): they act on the sums /
+  // differences of mirrored cells, HS resp. HS-1 terms instead of ORD.
+  double sm[NV][HS], df[NV][HS];
+  if constexpr (M::is_const) {
+#pragma unroll
+    for (int v = 0; v < NV; v++) {
+#pragma unroll
+      for (int k = 0; k < HS - 1; k++) { sm[v][k] = u[v][ORD - 1 - k] + u[v][k]; df[v][k] = u[v][ORD - 1 - k] - u[v][k]; }
+      sm[v][HS - 1] = u[v][HS - 1];
     }
   }
 #pragma unroll
-  for (int ii = 0; ii < ORD; ii++) {
+  for (int r = 0; r < ORD; r++) {
     double t[NV];
+    bool started = false;
+    if constexpr (M::is_const) {
+      const bool even = C::hi_even(r);
 #pragma unroll
-    for (int v = 0; v < NV; v++) t[v] = m.br(0, ii) * u[v][0];
+      for (int k = 0; k < HS; k++) {
+        if (!even && k == HS - 1) continue;
+        if (!nonzero_hi(m, r, ORD - 1 - k)) continue;
 #pragma unroll
-    for (int s = 1; s < ORD; s++) {
-      if (nonzero_br(m, s, ii)) {
+        for (int v = 0; v < NV; v++) {
+          const double x = even ? sm[v][k] : df[v][k];
+          t[v] = started ? fma(m.hi(r, ORD - 1 - k), x, t[v]) : m.hi(r, ORD - 1 - k) * x;
+        }
+        started = true;
+      }
+    } else {
 #pragma unroll
-        for (int v = 0; v < NV; v++) t[v] = fma(m.br(s, ii), u[v][s], t[v]);
+      for (int s = 0; s < ORD; s++) {
+#pragma unroll
+        for (int v = 0; v < NV; v++) t[v] = started ? fma(m.hi(r, s), u[v][s], t[v]) : m.hi(r, s) * u[v][s];
+        started = true;
       }
     }
 #pragma unroll
-    for (int v = 0; v < NV; v++) ab[v][ii] = t[v];
+    for (int v = 0; v < NV; v++) {
+      if (r == 0) e[v][HS] = t[v];
+      else if (r == 1) { o2[v][HS] = t[v]; tv[v][HS] = t[v] * t[v]; }
+      else tv[v][HS] = fma(t[v], t[v], tv[v][HS]);
+    }
   }
   const double eps = C::eps();
 #pragma unroll
   for (int v = 0; v < NV; v++) {
-    double tv[N];
+    double tl[HS];
 #pragma unroll
-    for (int i = 0; i < HS; i++) tv[i] = C::tv_lo(alo[v][i]);
-    tv[HS] = C::tv_hi(ab[v]);
-    double avg = tv[0];
-#pragma unroll
-    for (int i = 1; i < HS; i++) avg += tv[i];
-    avg *= C::rhs();
-    tv[HS] = fma(tv[HS] - avg, C::sigma(), avg);
+    for (int i = 0; i < HS; i++) tl[i] = tv[v][i];
+    const double avg = tree_sum<HS>(tl) * C::rhs();
+    tv[v][HS] = fma(tv[v][HS] - avg, C::sigma(), avg);
     // Weights (WenoLimiter.h:142-166): w_i = idl_i/(tv_i^2+eps); convexify; map_weights; convexify. Both normalisations
     // are carried out over a common denominator -- w_i/(sum_j w_j + eps) = idl_i P_i / (sum_j idl_j P_j + eps P) with
     // P_i = prod_{j!=i}(tv_j^2+eps), P = prod_j(tv_j^2+eps) -- the same rational expression evaluated with two
@@ -230,12 +267,11 @@ __device__ __forceinline__ void weno_EO_n(const double (&u)[NV][ORD], const M &m
     // products neither overflow nor underflow in FP64).
     double t[N], pr[N], x[N];
 #pragma unroll
-    for (int i = 0; i < N; i++) t[i] = fma(tv[i], tv[i], eps);
+    for (int i = 0; i < N; i++) t[i] = fma(tv[v][i], tv[v][i], eps);
     others_product<N>(t, pr);
-    double sum = eps * (pr[0] * t[0]);
 #pragma unroll
-    for (int i = 0; i < N; i++) { x[i] = C::idl(i) * pr[i]; sum += x[i]; }
-    const double r1 = rcp_pos(sum);
+    for (int i = 0; i < N; i++) x[i] = C::idl(i) * pr[i];
+    const double r1 = rcp_pos(fma(eps, pr[0] * t[0], tree_sum<N>(x)));
     double num[N];
 #pragma unroll
     for (int i = 0; i < N; i++) {
@@ -245,36 +281,15 @@ __device__ __forceinline__ void weno_EO_n(const double (&u)[NV][ORD], const M &m
       t[i] = fma(xi, C::map(i, 2), C::map(i, 3));
     }
     others_product<N>(t, pr);
-    double w[N], sum2 = eps * (pr[0] * t[0]);
+    double w[N];
 #pragma unroll
-    for (int i = 0; i < N; i++) { w[i] = num[i] * pr[i]; sum2 += w[i]; }
-    const double r2 = rcp_pos(sum2);
-    double Eb = 0.0, Ob = 0.0;
+    for (int i = 0; i < N; i++) w[i] = num[i] * pr[i];
+    const double r2 = rcp_pos(fma(eps, pr[0] * t[0], tree_sum<N>(w)));
+    double Eb = w[0] * e[v][0], Ob = w[0] * o2[v][0];
 #pragma unroll
-    for (int i = 0; i < HS; i++) {
-      double e = alo[v][i][0], o = 0.0;
-      double sc = 0.5;
-#pragma unroll
-      for (int s = 1; s < HS; s++) {
-        if (s & 1) o = fma(sc, alo[v][i][s], o); else e = fma(sc, alo[v][i][s], e);
-        sc *= 0.5;
-      }
-      Eb = fma(w[i], e, Eb);
-      Ob = fma(w[i], o, Ob);
-    }
-    {
-      double e = ab[v][0], o = 0.0;
-      double sc = 0.5;
-#pragma unroll
-      for (int s = 1; s < ORD; s++) {
-        if (s & 1) o = fma(sc, ab[v][s], o); else e = fma(sc, ab[v][s], e);
-        sc *= 0.5;
-      }
-      Eb = fma(w[HS], e, Eb);
-      Ob = fma(w[HS], o, Ob);
-    }
+    for (int i = 1; i < N; i++) { Eb = fma(w[i], e[v][i], Eb); Ob = fma(w[i], o2[v][i], Ob); }
     E[v] = Eb * r2;
-    O[v] = Ob * r2;
+    O[v] = Ob * (0.5 * r2);
   }
 }
 

@@ -89,6 +89,65 @@ def tv_terms(n):
     return [(i, j, c) for (i, j), c in sorted(terms.items(), key=lambda kv: (kv[0][1], kv[0][0])) if c != 0]
 
 
+def tv_rows(n):
+    """The truncated-TV quadratic form of an n-coefficient polynomial (tv_terms) factored as T = L D L^T (exact rational;
+    every D_k is positive for n <= 9) -> the matrix G (n x n) that maps coefficients a_0..a_{n-1} to
+        row 0   : e = sum_{even s} (1/2)^s a_s        (even part of the edge values: p(+-1/2) = e +- o)
+        row k>0 : p_k = sqrt(D_k) * sum_{j>=k} L[j][k] a_j     so that TV = sum_k p_k^2
+    and it turns out that p_1 = 2*o = sum_{odd s} 2 (1/2)^s a_s for every n (checked below), so the odd part of the edge
+    values needs no row of its own. Entries are returned as (Fraction r, Fraction d) meaning r*sqrt(d)."""
+    m = n - 1
+    T = [[F(0)] * m for _ in range(m)]
+    for i, j, c in tv_terms(n):
+        if i == j:
+            T[i - 1][j - 1] = c
+        else:
+            T[i - 1][j - 1] = T[j - 1][i - 1] = c / 2
+    L = [[F(int(i == j)) for j in range(m)] for i in range(m)]
+    D = [F(0)] * m
+    for j in range(m):
+        D[j] = T[j][j] - sum(L[j][k] ** 2 * D[k] for k in range(j))
+        assert D[j] > 0
+        for i in range(j + 1, m):
+            L[i][j] = (T[i][j] - sum(L[i][k] * L[j][k] * D[k] for k in range(j))) / D[j]
+    # 2*o in terms of p: solve L y = c  ->  2o = sum_k y_k/sqrt(D_k) p_k ; must be (1, 0, 0, ...) with D_1 = 1
+    c = [F(2) * F(1, 2) ** s if s % 2 else F(0) for s in range(1, n)]
+    y = [F(0)] * m
+    for i in range(m):
+        y[i] = c[i] - sum(L[i][k] * y[k] for k in range(i))
+    assert D[0] == 1 and y[0] == 1 and all(v == 0 for v in y[1:]), "p_1 != 2*o"
+    G = [[(F(0), F(1))] * n for _ in range(n)]
+    G[0] = [(F(1, 2) ** s if s % 2 == 0 else F(0), F(1)) for s in range(n)]
+    for k in range(1, n):
+        G[k] = [(L[j - 1][k - 1] if j >= k else F(0), D[k - 1]) for j in range(n)]
+        G[k][0] = (F(0), F(1))
+    return G
+
+
+def mp_rows(G, M):
+    """R[r][s] = sum_ii G[r][ii] * M[s][ii] in 60-digit arithmetic (G entries r*sqrt(d)); returns mpmath values"""
+    import mpmath
+    mpmath.mp.dps = 60
+    n = len(G)
+    ns = len(M)
+    out = []
+    for r in range(n):
+        row = []
+        for s in range(ns):
+            acc = F(0)
+            d = G[r][1][1] if n > 1 else F(1)
+            for ii in range(n):
+                acc += G[r][ii][0] * M[s][ii]
+            dd = G[r][-1][1]
+            row.append(mpmath.mpf(acc.numerator) / mpmath.mpf(acc.denominator) * mpmath.sqrt(mpmath.mpf(dd.numerator) / mpmath.mpf(dd.denominator)))
+        out.append(row)
+    return out
+
+
+def mpd(x):
+    return float(x).hex()
+
+
 def dbl(fr):
     """nearest double of a Fraction as a C hex-float literal (exact, no decimal round trip)"""
     x = fr.numerator / fr.denominator if isinstance(fr, F) else float(fr)   # int/int is correctly rounded
@@ -144,6 +203,28 @@ def emit(guard):
         w("#define AWFL_WRL_%d_INIT {%s}" % (o, ", ".join("{" + ", ".join("{" + ", ".join(dbl(W[i][s][ii]) for ii in range(m)) + "}" for s in range(m)) + "}" for i in range(m))))
         w("#define AWFL_BRIDGE_%d_INIT {%s}" % (o, ", ".join("{" + ", ".join(dbl(B[s][ii]) for ii in range(o)) + "}" for s in range(o))))
         w("#define AWFL_IDL_%d_INIT {%s}" % (o, ", ".join(float(x).hex() for x in idl)))
+        # --- "row" form used by the marching kernels: every candidate polynomial is reduced, by ONE matrix applied to its
+        # stencil, to the even part e of its edge values and the TV factors p_1..p_{n-1} (TV = sum p_k^2, odd part
+        # o = p_1/2): RLO[i][r][s] for the low-order stencils, RHI[r][s] for the bridge polynomial. GLO/GHI are the
+        # same maps in coefficient space (the host applies them to the per-level vertical matrices).
+        Glo, Ghi = tv_rows(m), tv_rows(o)
+        Wd = [[[F(float.fromhex(dbl(W[i][s][ii]))) for ii in range(m)] for s in range(m)] for i in range(m)]
+        RLO = [mp_rows(Glo, Wd[i]) for i in range(m)]
+        RHI = mp_rows(Ghi, B)
+        par = []
+        for r in range(o):
+            ev = all(abs(RHI[r][s] - RHI[r][o - 1 - s]) < 1e-45 for s in range(o))
+            od = all(abs(RHI[r][s] + RHI[r][o - 1 - s]) < 1e-45 for s in range(o))
+            assert ev != od, "bridge row %d of ord %d is neither even nor odd" % (r, o)
+            par.append(1 if ev else -1)
+        import mpmath
+        def gval(e):
+            return mpmath.mpf(e[0].numerator) / mpmath.mpf(e[0].denominator) * mpmath.sqrt(mpmath.mpf(e[1].numerator) / mpmath.mpf(e[1].denominator))
+        w("#define AWFL_GLO_%d_INIT {%s}" % (o, ", ".join("{" + ", ".join(mpd(gval(Glo[r][ii])) for ii in range(m)) + "}" for r in range(m))))
+        w("#define AWFL_GHI_%d_INIT {%s}" % (o, ", ".join("{" + ", ".join(mpd(gval(Ghi[r][ii])) for ii in range(o)) + "}" for r in range(o))))
+        w("#define AWFL_RLO_%d_INIT {%s}" % (o, ", ".join("{" + ", ".join("{" + ", ".join(mpd(RLO[i][r][s]) for s in range(m)) + "}" for r in range(m)) + "}" for i in range(m))))
+        w("#define AWFL_RHI_%d_INIT {%s}" % (o, ", ".join("{" + ", ".join(mpd(RHI[r][s]) for s in range(o)) + "}" for r in range(o))))
+        w("#define AWFL_RHI_PAR_%d_INIT {%s}" % (o, ", ".join(str(x) for x in par)))
         w("AWFL_TBL_QUAL double AWFL_SIGMA_%d = %s;" % (o, SIGMA[o]))
         for tag, n in (("LO", m), ("HI", o)):
             t = tv_terms(n)

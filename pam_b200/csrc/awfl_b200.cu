@@ -23,6 +23,10 @@
 #include "awfl_tables.h"
 #include "awfl_types.h"
 
+#ifndef AWFL_FCT_STRIP
+#define AWFL_FCT_STRIP 4
+#endif
+
 namespace awfl {
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -150,6 +154,125 @@ __global__ void __launch_bounds__(256) k_tracer_update(const Geom g, const Trace
   v += a.c * tend;
   if (a.positive[tr]) v = fmax(0.0, v);
   a.qout[(NS + tr) * nc + cell] = v;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// 2-D fused form of the two kernels above (k_fct_mult + k_tracer_update): one warp = 32 members x a strip of W columns,
+// marching up a segment of levels. A level's FCT multipliers are computed for the strip and its two halo columns from
+// loads that stay in registers, used at once for the x faces and the lower z face of that level, and carried one level
+// for its upper z face -- the multiplier field is never written, the tracer fluxes and the two tracer states are read
+// once (plus the halo columns, which the neighbouring strip reads anyway: L2). 5 doubles per (cell, tracer) of HBM
+// traffic instead of 12. Same formulas as the two kernels (which remain the 3-D path and the tendency entry point).
+// ---------------------------------------------------------------------------------------------------------------
+struct FctUpdArgs {
+  const double *q0, *qs;   // step-start and stage-input state (N fields)
+  double *qout;            // stage output state (N fields)
+  const double *tfx, *tfz, *dz, *rdz;
+  const unsigned char *positive;
+  double a, b, c;          // stage combination: out = a*q0 + b*qs + c*tend; FCT start mass = a*q0 + b*qs
+  double dt;               // stage time step of the FCT mass budget
+  double rdx;
+  int ksegs;               // level segments per column
+};
+
+__device__ __forceinline__ double rcp_pos_b(double x) {   // same as awfl_weno.cuh rcp_pos
+  double r;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
+  const double e = fma(-x, r, 1.0);
+  return fma(r, fma(e, e, e), r);
+}
+
+template <int W>
+__global__ void __launch_bounds__(32, W <= 4 ? 16 : 10) k_fct_update_2d(const Geom g, const FctUpdArgs a) {
+  const int e = g.e0 + (int)blockIdx.x * 32 + (int)threadIdx.x;
+  if (e >= g.e0 + g.ne) return;
+  const int i0 = (int)blockIdx.y * W;
+  const int tr = (int)(blockIdx.z / (unsigned)a.ksegs), seg = (int)(blockIdx.z - (unsigned)tr * (unsigned)a.ksegs);
+  const int k0 = (seg * g.nz) / a.ksegs, k1 = ((seg + 1) * g.nz) / a.ksegs;
+  const long nc = g.ncell, sz = (long)g.nx * g.nens;
+  const double *__restrict__ fx = a.tfx + tr * nc;
+  const double *__restrict__ fz = a.tfz + tr * (nc + sz);
+  const double *__restrict__ q0 = a.q0 + (NS + tr) * nc;
+  const double *__restrict__ qs = a.qs + (NS + tr) * nc;
+  double *__restrict__ qo = a.qout + (NS + tr) * nc;
+  const bool positive = a.positive[tr] != 0;
+  // column offsets of the strip, its halo columns (-1, W) and the interface beyond (W+1), periodic in x
+  long off[W + 3];
+#pragma unroll
+  for (int c = 0; c < W + 3; c++) {
+    const int i = ((i0 + c - 1) % g.nx + g.nx) % g.nx;      // once per thread; a ragged last strip can run past the seam
+    off[c] = (long)i * g.nens + e;
+  }
+  const int kstart = k0 > 0 ? k0 - 1 : 0;
+  double A[W + 2], Mp[W], P[W];       // carried: z fluxes of the interface below the level, multipliers and partial result of the level below
+  double crdz_prev = 0.0;
+#pragma unroll
+  for (int c = 0; c < W + 2; c++) A[c] = __ldg(fz + (long)kstart * sz + off[c]);
+#pragma unroll
+  for (int c = 0; c < W; c++) { Mp[c] = 1.0; P[c] = 0.0; }
+#pragma unroll 1
+  for (int kk = kstart; kk <= k1; kk++) {
+    const bool inside = kk < g.nz;
+    const long lv = (long)kk * sz;
+    double M[W + 2], X[W + 3], B[W + 2], V[W + 2];
+    double dzk = 1.0, rdzk = 0.0;
+    if (inside) {
+      dzk = __ldg(a.dz + (long)kk * g.nens + e); rdzk = __ldg(a.rdz + (long)kk * g.nens + e);
+#pragma unroll
+      for (int c = 0; c < W + 3; c++) X[c] = __ldg(fx + lv + off[c]);
+#pragma unroll
+      for (int c = 0; c < W + 2; c++) B[c] = __ldg(fz + lv + sz + off[c]);
+#pragma unroll
+      for (int c = 0; c < W + 2; c++) V[c] = a.b * __ldg(qs + lv + off[c]);
+      if (a.a != 0.0) {
+#pragma unroll
+        for (int c = 0; c < W + 2; c++) V[c] = fma(a.a, q0[lv + off[c]], V[c]);   // plain load: qout may alias q0
+      }
+      const double vol = g.dx * g.dy * dzk;
+#pragma unroll
+      for (int c = 0; c < W + 2; c++) {
+        double m = 1.0;
+        if (positive) {
+          const double avail = fmax(V[c], 0.0) * vol;
+          const double ox = (fmax(X[c + 1], 0.0) - fmin(X[c], 0.0)) * a.rdx;
+          const double oz = (fmax(B[c], 0.0) - fmin(A[c], 0.0)) * rdzk;
+          const double out = (ox + oz) * a.dt * vol;
+          // avail/out as a reciprocal-multiply (MUFU seed + one cubic step, <= 1 ulp; no divergent slow path). The clamp
+          // keeps the seed in the normal range; below it avail < out < 1e-290 and the product is still < 1.
+          if (out > avail) m = avail * rcp_pos_b(fmax(out, 1.0e-290));
+        }
+        M[c] = m;
+      }
+    } else {
+#pragma unroll
+      for (int c = 0; c < W + 2; c++) { M[c] = 1.0; B[c] = 0.0; V[c] = 0.0; }
+#pragma unroll
+      for (int c = 0; c < W + 3; c++) X[c] = 0.0;
+    }
+    const bool finish = kk - 1 >= k0, start = kk >= k0 && kk < k1;
+    const double crdz = a.c * rdzk, crdx = a.c * a.rdx;
+#pragma unroll
+    for (int c = 0; c < W; c++) {
+      const int i = i0 + c;
+      if (i >= g.nx) continue;
+      // interface kk: upper face of level kk-1, lower face of level kk
+      const double hA = fct_scaled(A[c + 1], kk > 0 ? Mp[c] : 1.0, M[c + 1], false);
+      if (finish) {
+        double v = fma(-crdz_prev, hA, P[c]);
+        if (positive) v = fmax(0.0, v);
+        qo[lv - sz + off[c + 1]] = v;
+      }
+      if (start) {
+        const double f0 = fct_scaled(X[c + 1], M[c], M[c + 1], i == 0);
+        const double f1 = fct_scaled(X[c + 2], M[c + 1], M[c + 2], i == g.nx - 1);
+        P[c] = fma(crdz, hA, fma(-crdx, f1 - f0, V[c + 1]));
+      }
+      Mp[c] = M[c + 1];
+    }
+#pragma unroll
+    for (int c = 0; c < W + 2; c++) A[c] = B[c];
+    crdz_prev = crdz;
+  }
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -345,6 +468,7 @@ struct awfl_handle {
   double *stage_fields;  // staging buffer for the host-buffer entry point (5+nt fields)
   int host_last_ncycles;      // sub-cycle count derived by the previous awfl_time_step_host (0 = none yet): the prediction
   long host_mispredictions;   // calls whose prediction was wrong and were redone un-overlapped
+  bool fused_fct;        // 2-D: fused FCT + tracer update kernel (AWFL_FUSED_FCT=0 selects the two-kernel path)
   int host_slabs;        // member slabs of the host-buffer entry point (copy/compute overlap); 1 = no pipelining
   cudaStream_t s_in, s_out;              // copy streams of the host-buffer entry point
   std::vector<cudaEvent_t> slab_ev;      // 2 events per slab: inputs on the device / results ready on the device
@@ -579,7 +703,22 @@ static void run_stage(awfl_handle *h, const Geom &g, const double *qin, const do
     t.qin = qin; t.mflux = h->mflux[dir]; t.tflux = h->tflux[dir]; t.vtab = h->vtab; t.vst = s.vst; t.sbits = s.sbits; t.labits = s.labits;
     launch_tracer_sweep(h, g, dir, t);
   }
-  if (g.nt > 0) {
+  if (g.nt > 0 && g.sim2d && mode == 1 && !fct_start && h->fused_fct) {
+    // fused FCT + update (2-D): strips of W columns, enough level segments for a few waves of one-warp blocks
+    constexpr int W = AWFL_FCT_STRIP;
+    FctUpdArgs u;
+    u.q0 = q0; u.qs = qin; u.qout = qout; u.tfx = h->tflux[0]; u.tfz = h->tflux[2]; u.dz = h->dz; u.rdz = h->rdz;
+    u.positive = h->positive_d; u.a = a; u.b = b; u.c = b * dt_full; u.dt = dt_stage; u.rdx = 1.0 / g.dx;
+    const unsigned tiles = (unsigned)(g.ne + 31) / 32, strips = (unsigned)(g.nx + W - 1) / W;
+    const long per_seg = (long)tiles * strips * g.nt;
+    long ks = (16000 + per_seg - 1) / per_seg;
+    if (ks > g.nz / 8) ks = g.nz / 8;
+    if (ks < 1) ks = 1;
+    if (const char *ev = getenv("AWFL_FCT_KSEGS")) { const int v = atoi(ev); if (v >= 1 && v <= g.nz) ks = v; }   // experiments
+    u.ksegs = (int)ks;
+    ProfScope ps(h, KC_TRACER_UPD);
+    k_fct_update_2d<W><<<dim3(tiles, strips, (unsigned)(g.nt * ks)), 32, 0, h->stream>>>(g, u);
+  } else if (g.nt > 0) {
     const RowMap rm = row_map(g, 256);
     const unsigned blocks = row_blocks(g, rm);
     FctArgs f;
@@ -682,6 +821,7 @@ int awfl_create(const awfl_config *cfg, awfl_handle **out) {
   ALLOC(h->positive_d, nt); ALLOC(h->adds_mass_d, nt);
   ALLOC(h->trptr_d, sizeof(double *) * nt);
   h->stage_fields = nullptr; h->tmp_state = nullptr;
+  { const char *ev = getenv("AWFL_FUSED_FCT"); h->fused_fct = !(ev && atoi(ev) == 0); }
   h->s_in = nullptr; h->s_out = nullptr; h->host_last_ncycles = 0; h->host_mispredictions = 0;
   {
     // member slabs of awfl_time_step_host: 4 by default (measured on C2); AWFL_HOST_SLABS overrides
@@ -808,20 +948,27 @@ static int step_ncycles(awfl_handle *h, double crm_dt, int *ncycles, cudaStream_
   *ncycles = (int)ceil(crm_dt / dt_dyn);
   return 0;
 }
-// (3) ncycles SSPRK3 sub-cycles (Dycore.h:147-222; Q0 = step state, Q1/Q2 = stage states)
-static void step_advance(awfl_handle *h, const Geom &g, int ncycles, double dt) {
-  for (int c = 0; c < ncycles; c++) {
-    run_stage(h, g, h->Q[0], h->Q[0], h->Q[1], 0.0, 1.0, dt, dt, 1.0, 0.0, 1, nullptr, nullptr, nullptr);
-    run_stage(h, g, h->Q[1], h->Q[0], h->Q[2], 3.0 / 4.0, 1.0 / 4.0, (1.0 / 4.0) * dt, dt, 3.0 / 4.0, 1.0 / 4.0, 1, nullptr, nullptr, nullptr);
-    run_stage(h, g, h->Q[2], h->Q[0], h->Q[0], 1.0 / 3.0, 2.0 / 3.0, (2.0 / 3.0) * dt, dt, 1.0 / 3.0, 2.0 / 3.0, 1, nullptr, nullptr, nullptr);
+// (3) ncycles SSPRK3 sub-cycles (Dycore.h:147-222). The step state enters in Q[0]; the three buffers rotate -- stage 1:
+// C -> S1, stage 2: S1 (+C) -> S2, stage 3: S2 (+C) -> S1, which becomes the next C -- so that no stage writes the buffer
+// another block of the same launch still reads (the fused FCT kernel reads halo columns of the step-start tracers).
+// Returns the index of the buffer that holds the result.
+static int step_advance(awfl_handle *h, const Geom &g, int ncycles, double dt) {
+  int c = 0;
+  for (int n = 0; n < ncycles; n++) {
+    const int s1 = (c + 1) % 3, s2 = (c + 2) % 3;
+    run_stage(h, g, h->Q[c], h->Q[c], h->Q[s1], 0.0, 1.0, dt, dt, 1.0, 0.0, 1, nullptr, nullptr, nullptr);
+    run_stage(h, g, h->Q[s1], h->Q[c], h->Q[s2], 3.0 / 4.0, 1.0 / 4.0, (1.0 / 4.0) * dt, dt, 3.0 / 4.0, 1.0 / 4.0, 1, nullptr, nullptr, nullptr);
+    run_stage(h, g, h->Q[s2], h->Q[c], h->Q[s1], 1.0 / 3.0, 2.0 / 3.0, (2.0 / 3.0) * dt, dt, 1.0 / 3.0, 2.0 / 3.0, 1, nullptr, nullptr, nullptr);
+    c = s1;
   }
+  return c;
 }
 // (4) convert_dynamics_to_coupler (Dycore.h:1281-1331)
-static void step_convert_out(awfl_handle *h, const Geom &g, const FieldPtrs &fp, cudaStream_t st = nullptr) {
+static void step_convert_out(awfl_handle *h, const Geom &g, const FieldPtrs &fp, int qi, cudaStream_t st = nullptr) {
   if (!st) st = h->stream;
   ProfScope ps(h, KC_OUT, st);
   const RowMap rm = row_map(g, 256);
-  k_dycore_to_coupler<<<row_blocks(g, rm), 256, 0, st>>>(g, h->ph, fp, h->cfg.idWV, h->adds_mass_d, h->Q[0], rm);
+  k_dycore_to_coupler<<<row_blocks(g, rm), 256, 0, st>>>(g, h->ph, fp, h->cfg.idWV, h->adds_mass_d, h->Q[qi], rm);
 }
 
 int awfl_time_step(awfl_handle *h, const awfl_fields *f, double crm_dt, int ncycles_override, int *ncycles_out) {
@@ -839,8 +986,8 @@ int awfl_time_step(awfl_handle *h, const awfl_fields *f, double crm_dt, int ncyc
   if (need_dt && step_ncycles(h, crm_dt, &ncycles)) return 1;
   const double dt = crm_dt / ncycles;       // Dycore.h:145
   if (ensure_cvtab(h)) return 1;
-  step_advance(h, g, ncycles, dt);
-  step_convert_out(h, g, fp);
+  const int qi = step_advance(h, g, ncycles, dt);
+  step_convert_out(h, g, fp, qi);
   CK(cudaGetLastError());
   if (ncycles_out) *ncycles_out = ncycles;
   return 0;
@@ -900,6 +1047,7 @@ int awfl_time_step_host(awfl_handle *h, double *const *host_fields, double crm_d
   CK(cudaEventRecord(h->slab_ev[2 * P], h->stream));
   CK(cudaStreamWaitEvent(h->s_in, h->slab_ev[2 * P], 0));
   const int predicted = need_dt ? h->host_last_ncycles : ncycles_override;
+  int qi = 0;   // buffer that holds the advanced state (the same for every slab: it depends on the sub-cycle count only)
   std::vector<Geom> slab(P, g);
   const size_t rows = (size_t)g.nz * g.ny * g.nx, pitch = sizeof(double) * (size_t)g.nens;
   for (int s = 0; s < P; s++) {
@@ -915,7 +1063,7 @@ int awfl_time_step_host(awfl_handle *h, double *const *host_fields, double crm_d
     CK(cudaEventRecord(h->slab_ev[2 * s], h->s_in));
     if (predicted > 0) {
       CK(cudaStreamWaitEvent(h->stream, h->slab_ev[2 * s], 0));
-      step_advance(h, slab[s], predicted, crm_dt / predicted);
+      qi = step_advance(h, slab[s], predicted, crm_dt / predicted);
       CK(cudaEventRecord(h->slab_ev[2 * s + 1], h->stream));
     }
   }
@@ -927,8 +1075,8 @@ int awfl_time_step_host(awfl_handle *h, double *const *host_fields, double crm_d
     // misprediction: redo the whole step from the staged inputs (still intact), un-overlapped
     h->host_mispredictions++;
     step_convert_in(h, g, fp, false);
-    step_advance(h, g, ncycles, dt);
-    step_convert_out(h, g, fp);
+    qi = step_advance(h, g, ncycles, dt);
+    step_convert_out(h, g, fp, qi);
     CK(cudaEventRecord(h->slab_ev[1], h->stream));
     CK(cudaStreamWaitEvent(h->s_out, h->slab_ev[1], 0));
     for (int v = 0; v < N; v++) CK(cudaMemcpyAsync(host_fields[v], h->stage_fields + (size_t)v * g.ncell, fb, cudaMemcpyDeviceToHost, h->s_out));
@@ -936,11 +1084,11 @@ int awfl_time_step_host(awfl_handle *h, double *const *host_fields, double crm_d
     for (int s = 0; s < P; s++) {
       if (predicted <= 0) {
         if (s == 0) CK(cudaStreamWaitEvent(h->stream, h->slab_ev[2 * (P - 1)], 0));
-        step_advance(h, slab[s], ncycles, dt);
+        qi = step_advance(h, slab[s], ncycles, dt);
         CK(cudaEventRecord(h->slab_ev[2 * s + 1], h->stream));
       }
       CK(cudaStreamWaitEvent(h->s_out, h->slab_ev[2 * s + 1], 0));
-      step_convert_out(h, slab[s], fp, h->s_out);
+      step_convert_out(h, slab[s], fp, qi, h->s_out);
       for (int v = 0; v < N; v++) {
         if (P == 1) CK(cudaMemcpyAsync(host_fields[v], h->stage_fields + (size_t)v * g.ncell, fb, cudaMemcpyDeviceToHost, h->s_out));
         else CK(cudaMemcpy2DAsync(host_fields[v] + slab[s].e0, pitch, h->stage_fields + (size_t)v * g.ncell + slab[s].e0, pitch,

@@ -94,7 +94,7 @@ def _sc_qv(z, ztop, R_d, grav):
     T = _sc_temperature(z, ztop)
     pd = _sc_pressure_dry(z, ztop, R_d, grav)
     qvs = 380.0 / pd * np.exp(17.27 * (T - 273.0) / (T - 36.0))
-    rh = np.where(z <= 12000.0, 1.0 - 0.75 * np.power(np.minimum(z, 12000.0) / 12000.0, 1.25), 0.25)
+    rh = np.where(z <= 12000.0, 1.0 - 0.75 * np.power(np.clip(z, 0.0, 12000.0) / 12000.0, 1.25), 0.25)   # z can round to -1e-13 at the surface
     return np.minimum(0.014, qvs * rh), T
 
 

@@ -231,6 +231,30 @@ def test_host_buffer_member_slabs_are_bit_identical(nens, slabs, ny):
         assert np.array_equal(a, got[n]), n
 
 
+@pytest.mark.parametrize("nx,nz,nens", [(10, 12, 40), (5, 9, 33), (24, 20, 64)])
+def test_fused_fct_update_matches_two_kernel_path(nx, nz, nens, monkeypatch):
+    """2-D: the fused FCT + tracer update strip march (k_fct_update_2d) against the two cell-local kernels it replaces
+    (k_fct_mult + k_tracer_update, still the 3-D path): same formulas, different summation order -> equal to round-off.
+    P3+SHOC tracer set with exact zeros over a third of the cells so that the limiter actually scales fluxes; strips that
+    are ragged (nx not a multiple of 8) or wider than the domain (nx < 8) and level segments are exercised."""
+    case = syn.make_case(nz, 1, nx, nens, tracers=syn.TRACERS_P3_SHOC, grid="tanh")
+    out = {}
+    for fused in ("1", "0"):
+        monkeypatch.setenv("AWFL_FUSED_FCT", fused)
+        c, d = H.make_gpu(case, 5, crm_dt=3.0)
+        d.declare_current_profile_as_hydrostatic(c)
+        for _ in range(3):
+            d.timeStep(c)
+        out[fused] = H.gpu_fields(c)
+    un = float(np.linalg.norm(out["0"]["uvel"]))
+    for k in out["0"]:
+        a, b = out["1"][k], out["0"][k]
+        floor = 1e-3 * un if k in ("uvel", "vvel", "wvel") else 1e-300
+        assert np.linalg.norm(a - b) <= 1e-13 * max(np.linalg.norm(b), floor), k
+        if k not in H.STATE_FIELDS:
+            assert a.min() >= 0.0, k
+
+
 def test_errors_are_reported_not_swallowed():
     from pam_b200 import PamCoupler, Dycore
     c = PamCoupler("cuda:0")

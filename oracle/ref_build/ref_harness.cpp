@@ -21,6 +21,9 @@
 
 #include "pam_coupler.h"
 #include "Dycore.h"
+#include "sponge_layer.h"
+#include "gcm_forcing.h"
+#include "perturb_temperature.h"
 #include <cstring>
 #include <sstream>
 #include <chrono>
@@ -433,6 +436,41 @@ int ref_compute_mass(void *hv, double *out) {
     std::memcpy(out, m.data(), (size_t)(nt+2)*nens*sizeof(double));
     return 0;
   } catch (...) { return 1; }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// Coupler modules either side of the dycore: the reference's own functions on the
+// handle's coupler. Options they read are set through ref_set_option_real / _int.
+//   modules::sponge_layer                    pam_core/modules/sponge_layer.h:9-96
+//   modules::compute_gcm_forcing_tendencies  pam_core/modules/gcm_forcing.h:18-205
+//   modules::apply_gcm_forcing_tendencies    pam_core/modules/gcm_forcing.h:294-436 (+ fill_holes :208-289)
+//   modules::perturb_temperature             pam_core/modules/perturb_temperature.h:10-63
+// ---------------------------------------------------------------------------------------------------
+void ref_set_option_real(void *hv, const char *name, double v) { ((Handle*)hv)->coupler.set_option<real>(name, v); }
+void ref_set_option_int (void *hv, const char *name, int v)    { ((Handle*)hv)->coupler.set_option<int>(name, v); }
+int ref_entry_exists(void *hv, const char *name) {
+  return ((Handle*)hv)->coupler.get_data_manager_device_readwrite().entry_exists(name) ? 1 : 0;
+}
+int ref_sponge_layer(void *hv) {
+  try { modules::sponge_layer(((Handle*)hv)->coupler); return 0; }
+  catch (std::string &s) { std::cerr << "ref_sponge_layer: " << s << std::endl; return 1; } catch (...) { return 1; }
+}
+int ref_compute_gcm_forcing_tendencies(void *hv) {
+  try { modules::compute_gcm_forcing_tendencies(((Handle*)hv)->coupler); return 0; }
+  catch (std::string &s) { std::cerr << "ref_compute_gcm_forcing_tendencies: " << s << std::endl; return 1; } catch (...) { return 1; }
+}
+int ref_apply_gcm_forcing_tendencies(void *hv) {
+  try { modules::apply_gcm_forcing_tendencies(((Handle*)hv)->coupler); return 0; }
+  catch (std::string &s) { std::cerr << "ref_apply_gcm_forcing_tendencies: " << s << std::endl; return 1; } catch (...) { return 1; }
+}
+int ref_perturb_temperature(void *hv, const int *ids, double magnitude) {
+  Handle &h = *(Handle*)hv;
+  try {
+    int1d id("id", h.nens);
+    for (int e=0;e<h.nens;e++) id(e) = ids[e];
+    modules::perturb_temperature(h.coupler, id, magnitude);
+    return 0;
+  } catch (std::string &s) { std::cerr << "ref_perturb_temperature: " << s << std::endl; return 1; } catch (...) { return 1; }
 }
 
 // Wall-clock seconds for `nsteps` raw reference time steps (CPU baseline timing).

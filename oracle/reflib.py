@@ -62,6 +62,15 @@ def load(ord=5, omp=False):
     lib.ref_compute_mass.argtypes = [C.c_void_p, _dp]
     lib.ref_time_steps_raw.restype = C.c_double
     lib.ref_time_steps_raw.argtypes = [C.c_void_p, C.c_int]
+    lib.ref_set_option_real.argtypes = [C.c_void_p, C.c_char_p, C.c_double]
+    lib.ref_set_option_real.restype = None
+    lib.ref_set_option_int.argtypes = [C.c_void_p, C.c_char_p, C.c_int]
+    lib.ref_set_option_int.restype = None
+    lib.ref_entry_exists.argtypes = [C.c_void_p, C.c_char_p]
+    lib.ref_sponge_layer.argtypes = [C.c_void_p]
+    lib.ref_compute_gcm_forcing_tendencies.argtypes = [C.c_void_p]
+    lib.ref_apply_gcm_forcing_tendencies.argtypes = [C.c_void_p]
+    lib.ref_perturb_temperature.argtypes = [C.c_void_p, C.POINTER(C.c_int), C.c_double]
     lib.ref_shutdown.restype = None
     atexit.register(lib.ref_shutdown)
     _libs[key] = lib
@@ -140,6 +149,30 @@ class RefDycore:
 
     def get_fields(self):
         return {k: self.get_field(k) for k in list(STATE_FIELDS) + self.tracer_names}
+
+    # ---- coupler modules either side of the dycore: the reference's own functions ----
+    def set_option(self, name, value):
+        if isinstance(value, int):
+            self.lib.ref_set_option_int(self.h, name.encode(), value)
+        else:
+            self.lib.ref_set_option_real(self.h, name.encode(), float(value))
+
+    def entry_exists(self, name):
+        return bool(self.lib.ref_entry_exists(self.h, name.encode()))
+
+    def sponge_layer(self):
+        assert self.lib.ref_sponge_layer(self.h) == 0
+
+    def compute_gcm_forcing_tendencies(self):
+        assert self.lib.ref_compute_gcm_forcing_tendencies(self.h) == 0
+
+    def apply_gcm_forcing_tendencies(self):
+        assert self.lib.ref_apply_gcm_forcing_tendencies(self.h) == 0
+
+    def perturb_temperature(self, ids, magnitude=0.1):
+        a = np.ascontiguousarray(ids, dtype=np.int32)
+        assert a.size == self.nens
+        assert self.lib.ref_perturb_temperature(self.h, a.ctypes.data_as(C.POINTER(C.c_int)), float(magnitude)) == 0
 
     # ---- tables ----
     def tables(self):

@@ -89,7 +89,7 @@ class PamCoupler:
         self.dm.register_and_allocate("vertical_cell_dz", "", (nz, nens))
         self.dm.register_and_allocate("vertical_midpoint_height", "", (nz, nens))
         for n in ("gcm_density_dry", "gcm_uvel", "gcm_vvel", "gcm_wvel", "gcm_temp", "gcm_water_vapor",
-                  "gcm_cloud_water", "gcm_cloud_ice"):
+                  "gcm_cloud_water", "gcm_cloud_ice", "gcm_num_liq", "gcm_num_ice", "gcm_num_rain"):   # pam_coupler.h:268-281
             self.dm.register_and_allocate(n, "", (nz, nens))
 
     def set_grid(self, xlen, ylen, zint):

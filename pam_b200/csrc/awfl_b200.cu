@@ -66,6 +66,13 @@ __device__ __forceinline__ bool row_coords(const Geom &g, const RowMap m, long &
   return r < m.rowlen;
 }
 
+__device__ __forceinline__ double rcp_pos_b(double x) {   // same as awfl_weno.cuh rcp_pos
+  double r;
+  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
+  const double e = fma(-x, r, 1.0);
+  return fma(r, fma(e, e, e), r);
+}
+
 __global__ void __launch_bounds__(256) k_fct_mult(const Geom g, const FctArgs a, const RowMap rm) {
   long cell; int k, j, i, e;
   if (!row_coords(g, rm, cell, k, j, i, e)) return;
@@ -95,7 +102,8 @@ __global__ void __launch_bounds__(256) k_fct_mult(const Geom g, const FctArgs a,
     const double fz0 = __ldg(fz + cell), fz1 = __ldg(fz + cell + sz);
     const double oz = (fmax(fz1, 0.0) - fmin(fz0, 0.0)) * rdzk;
     const double out = (ox + oy + oz) * a.dt * vol;
-    if (out > avail) mult = avail / out;
+    // reciprocal-multiply (<= 1 ulp, no divergent slow path); the clamp keeps the seed in the normal range
+    if (out > avail) mult = avail * rcp_pos_b(fmax(out, 1.0e-290));
   }
   a.mult[tr * nc + cell] = mult;
 }
@@ -174,13 +182,6 @@ struct FctUpdArgs {
   double rdx;
   int ksegs;               // level segments per column
 };
-
-__device__ __forceinline__ double rcp_pos_b(double x) {   // same as awfl_weno.cuh rcp_pos
-  double r;
-  asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
-  const double e = fma(-x, r, 1.0);
-  return fma(r, fma(e, e, e), r);
-}
 
 template <int W>
 __global__ void __launch_bounds__(32, W <= 4 ? 16 : 10) k_fct_update_2d(const Geom g, const FctUpdArgs a) {

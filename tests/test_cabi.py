@@ -13,10 +13,13 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 HEADER = os.path.join(ROOT, "include", "awfl_b200.h")
 
 
-def _declared_functions():
-    src = open(HEADER).read()
+MODULES_HEADER = os.path.join(ROOT, "include", "pam_modules_b200.h")
+
+
+def _declared_functions(header=HEADER, prefix="awfl_"):
+    src = open(header).read()
     src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
-    names = re.findall(r"\b(awfl_[a-z0-9_]+)\s*\(", src)
+    names = re.findall(r"\b(%s[a-z0-9_]+)\s*\(" % prefix, src)
     return sorted(set(names))
 
 
@@ -46,6 +49,27 @@ def test_library_exports_every_declared_symbol():
     for fn in mod.EXPORTS:
         assert fn in _declared_functions(), "%s bound in _lib.py but not declared in the header" % fn
     assert lib.awfl_dycore_name().decode() == "SSPRK3+WENO+FV A-grid"    # Dycore.h:1544
+
+
+def test_library_exports_the_coupler_module_entry_points():
+    """include/pam_modules_b200.h: sponge layer, GCM forcing, temperature perturbation."""
+    mod, lib = _lib()
+    fns = _declared_functions(MODULES_HEADER, "pamm_")
+    for need in ("pamm_create", "pamm_destroy", "pamm_last_error", "pamm_sponge_layer", "pamm_compute_gcm_forcing_tendencies",
+                 "pamm_apply_gcm_forcing_tendencies", "pamm_perturb_temperature"):
+        assert need in fns
+    for fn in fns:
+        assert hasattr(lib, fn), "libawfl_b200.so does not export %s" % fn
+    text = open(MODULES_HEADER).read()
+    assert "sponge_layer.h:9-96" in text and "gcm_forcing.h:18-205" in text and "perturb_temperature.h:10-63" in text
+    import torch
+    if not torch.cuda.is_available():
+        h = C.c_void_p()
+        lib.pamm_create.argtypes = [C.c_int] * 5 + [C.c_void_p, C.POINTER(C.c_void_p)]
+        lib.pamm_last_error.restype = C.c_char_p
+        lib.pamm_last_error.argtypes = [C.c_void_p]
+        assert lib.pamm_create(4, 1, 4, 2, 0, None, C.byref(h)) != 0        # no device: fails, does not fall back
+        assert b"no CPU fallback" in lib.pamm_last_error(None)
 
 
 def test_library_contains_sm100a_kernels():

@@ -97,6 +97,12 @@ int awfl_compute_tendencies(awfl_handle *h, const double *state, const double *t
  * "variable_gravity" (nz,nens). gcm == NULL <=> use_gcm_data == false. Deterministic (no atomics). */
 int awfl_declare_hydrostatic(awfl_handle *h, const awfl_fields *f, const awfl_gcm_columns *gcm);
 
+/* The idealized initial states of Dycore::init (Dycore.h:985-1091, chosen there by "initData" of the standalone
+ * YAML file): data_spec 0 = rising thermal (:1017-1086), 1 = supercell sounding (Dycore::init_supercell,
+ * :1096-1276), each followed by convert_dynamics_to_coupler (:1281-1331): the coupler fields are overwritten.
+ * zint: DEVICE "vertical_interface_height" (nz+1,nens). Init-time call: allocates scratch and synchronises. */
+int awfl_init_idealized(awfl_handle *h, const awfl_fields *f, const double *zint, int data_spec);
+
 /* Dycore::compute_mass (Dycore.h:37-60): out_host[(num_tracers+2)*nens] = mean over cells of q*dz for each tracer,
  * rho and rho*theta. */
 int awfl_compute_mass(awfl_handle *h, const awfl_fields *f, double *out_host);

@@ -46,6 +46,14 @@ def load():
         _lib.pamo_apply_gcm_forcing_tendencies.restype = None
         _lib.pamo_perturb_temperature.argtypes = [C.c_int] * 4 + [_dp, C.POINTER(C.c_int), C.c_double]
         _lib.pamo_perturb_temperature.restype = None
+        _lib.pamo_gll9.argtypes = [_dp, _dp]
+        _lib.pamo_gll9.restype = None
+        _lib.pamo_init_supercell.argtypes = [C.c_int] * 4 + [C.c_double] * 2 + [_dp] + [C.c_double] * 5 + [C.c_int, C.c_int,
+                                                                                                         C.POINTER(C.c_int), C.POINTER(_dp)]
+        _lib.pamo_init_supercell.restype = None
+        _lib.pamo_init_thermal.argtypes = [C.c_int] * 4 + [C.c_double] * 2 + [_dp] + [C.c_double] * 7 + [C.c_int, C.c_int,
+                                                                                                       C.POINTER(C.c_int), C.POINTER(_dp)]
+        _lib.pamo_init_thermal.restype = None
     return _lib
 
 
@@ -98,3 +106,42 @@ def perturb_temperature(dm, ids, magnitude=0.1):
     nz, ny, nx, nens = _dims(dm)
     a = np.ascontiguousarray(ids, dtype=np.int32)
     load().pamo_perturb_temperature(nz, ny, nx, nens, _p(dm["temp"]), a.ctypes.data_as(C.POINTER(C.c_int)), float(magnitude))
+
+
+def gll9():
+    p, w = np.empty(9), np.empty(9)
+    load().pamo_gll9(_p(p), _p(w))
+    return p, w
+
+
+def derived_constants(consts):
+    """gamma_d, C0 the way Dycore::init derives them (Dycore.h:877-891)"""
+    R_d, cp_d, p0 = consts["R_d"], consts["cp_d"], consts["p0"]
+    cv_d = cp_d - R_d
+    gamma = cp_d / cv_d
+    kappa = R_d / cp_d
+    C0 = pow(R_d * pow(p0, -kappa), gamma)
+    return gamma, C0
+
+
+def init_idealized(kind, nz, ny, nx, nens, xlen, ylen, zint, tracers, consts, gamma, C0):
+    """Dycore::init's idealized data (kind = "supercell" | "thermal") -> {field name: array}; tracers as (name, positive, adds_mass)."""
+    z = np.asarray(zint, dtype=np.float64)
+    if z.ndim == 1:
+        z = np.repeat(z[:, None], nens, axis=1)
+    z = np.ascontiguousarray(z)
+    names = ["density_dry", "uvel", "vvel", "wvel", "temp"] + [t[0] for t in tracers]
+    out = {n: np.zeros((nz, ny, nx, nens)) for n in names}
+    ptrs = (_dp * len(names))(*[_p(out[n]) for n in names])
+    adds = (C.c_int * max(len(tracers), 1))(*[int(t[2]) for t in tracers])
+    idWV = [t[0] for t in tracers].index("water_vapor")
+    lib = load()
+    if kind == "supercell":
+        lib.pamo_init_supercell(nz, ny, nx, nens, float(xlen), float(ylen), _p(z), consts["R_d"], consts["R_v"], consts["grav"], gamma, C0,
+                                idWV, len(tracers), adds, ptrs)
+    elif kind == "thermal":
+        lib.pamo_init_thermal(nz, ny, nx, nens, float(xlen), float(ylen), _p(z), consts["R_d"], consts["R_v"], consts["cp_d"], consts["p0"],
+                              consts["grav"], gamma, C0, idWV, len(tracers), adds, ptrs)
+    else:
+        raise ValueError(kind)
+    return out

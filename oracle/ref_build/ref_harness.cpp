@@ -473,6 +473,88 @@ int ref_perturb_temperature(void *hv, const int *ids, double magnitude) {
   } catch (std::string &s) { std::cerr << "ref_perturb_temperature: " << s << std::endl; return 1; } catch (...) { return 1; }
 }
 
+// ---------------------------------------------------------------------------------------------------
+// Idealized initial states.
+//   ref_init_supercell : the reference's own Dycore::init_supercell (Dycore.h:1096-1276) followed by
+//                        convert_dynamics_to_coupler (:1281-1331), exactly what Dycore::init does for
+//                        initData = supercell (:1016, :1087).
+//   ref_init_thermal   : the DATA_SPEC_THERMAL branch of Dycore::init (:1017-1086) sits behind
+//                        PAM_STANDALONE + a YAML file and cannot be called on its own, so its two loops are
+//                        re-driven here around the reference's own point functions Dycore::hydro_const_theta
+//                        (:742) and Dycore::sample_ellipse_cosine (:757) and its GLL tables, then handed to
+//                        the reference's convert_dynamics_to_coupler.
+//   ref_gll9           : TransformMatrices::get_gll_points / get_gll_weights, 9 points.
+// ---------------------------------------------------------------------------------------------------
+void ref_gll9(double *pts, double *wts) {
+  SArray<real,1,9> p, w;
+  TransformMatrices::get_gll_points(p); TransformMatrices::get_gll_weights(w);
+  for (int i=0;i<9;i++) { pts[i] = p(i); wts[i] = w(i); }
+}
+int ref_init_supercell(void *hv) {
+  Handle &h = *(Handle*)hv;
+  int nz=h.nz, ny=h.ny, nx=h.nx, nens=h.nens, nt=h.nt;
+  try {
+    real5d state  ("state"  ,5 ,nz+2*HS,ny+2*HS,nx+2*HS,nens);
+    real5d tracers("tracers",nt,nz+2*HS,ny+2*HS,nx+2*HS,nens);
+    state = 0; tracers = 0;
+    h.dycore.init_supercell(h.coupler, state, tracers);
+    h.dycore.convert_dynamics_to_coupler(h.coupler, state, tracers);
+    return 0;
+  } catch (std::string &s) { std::cerr << "ref_init_supercell: " << s << std::endl; return 1; } catch (...) { return 1; }
+}
+int ref_init_thermal(void *hv) {
+  Handle &h = *(Handle*)hv;
+  auto &c = h.coupler;
+  int nz=h.nz, ny=h.ny, nx=h.nx, nens=h.nens, nt=h.nt;
+  try {
+    real R_d = c.get_option<real>("R_d"), cp_d = c.get_option<real>("cp_d"), p0 = c.get_option<real>("p0");
+    real grav = c.get_option<real>("grav"), gamma = c.get_option<real>("gamma_d"), C0 = c.get_option<real>("C0");
+    int idWV = c.get_option<int>("idWV");
+    real xlen = c.get_xlen(), ylen = c.get_ylen(), dx = c.get_dx(), dy = c.get_dy();
+    bool sim2d = ny == 1;
+    auto &dm = c.get_data_manager_device_readwrite();
+    auto dz   = dm.get<real const,2>("vertical_cell_dz");
+    auto zmid = dm.get<real const,2>("vertical_midpoint_height");
+    real5d state  ("state"  ,5 ,nz+2*HS,ny+2*HS,nx+2*HS,nens);
+    real5d tracers("tracers",nt,nz+2*HS,ny+2*HS,nx+2*HS,nens);
+    state = 0; tracers = 0;
+    real2d hy_dens_cells("hy_dens_cells",nz,nens), hy_pressure_cells("hy_pressure_cells",nz,nens);
+    const int nqpoints = 9;
+    SArray<real,1,nqpoints> qpoints, qweights;
+    TransformMatrices::get_gll_points(qpoints); TransformMatrices::get_gll_weights(qweights);
+    for (int k=0;k<nz;k++) for (int iens=0;iens<nens;iens++) {
+      hy_dens_cells(k,iens) = 0.; hy_pressure_cells(k,iens) = 0.;
+      for (int kk=0; kk<nqpoints; kk++) {
+        real z = zmid(k,iens) + qpoints(kk)*dz(k,iens);
+        real hr, ht;
+        Dycore::hydro_const_theta(z,grav,C0,cp_d,p0,gamma,R_d,hr,ht);
+        hy_dens_cells    (k,iens) += hr                       * qweights(kk);
+        hy_pressure_cells(k,iens) += C0*std::pow(hr*ht,gamma) * qweights(kk);
+      }
+    }
+    for (int k=0;k<nz;k++) for (int j=0;j<ny;j++) for (int i=0;i<nx;i++) for (int iens=0;iens<nens;iens++) {
+      for (int kk=0; kk<nqpoints; kk++) for (int jj=0; jj<nqpoints; jj++) for (int ii=0; ii<nqpoints; ii++) {
+        real x = (i+0.5)*dx + qpoints(ii)*dx;
+        real y = (j+0.5)*dy + qpoints(jj)*dy;   if (sim2d) y = ylen/2;
+        real z = zmid(k,iens) + qpoints(kk)*dz(k,iens);
+        real hr = hy_dens_cells(k,iens), hp = hy_pressure_cells(k,iens);
+        real ht = std::pow( hp/C0 , 1._fp/gamma ) / hr;
+        real rho = hr, u = 0, v = 0, w = 0, rho_v = 0;
+        real theta = ht + Dycore::sample_ellipse_cosine(2._fp , x,y,z , xlen/2,ylen/2,2000. , 2000.,2000.,2000.);
+        real wt = qweights(ii)*qweights(jj)*qweights(kk);
+        state(idR,HS+k,HS+j,HS+i,iens) += rho       * wt;
+        state(idU,HS+k,HS+j,HS+i,iens) += rho*u     * wt;
+        state(idV,HS+k,HS+j,HS+i,iens) += rho*v     * wt;
+        state(idW,HS+k,HS+j,HS+i,iens) += rho*w     * wt;
+        state(idT,HS+k,HS+j,HS+i,iens) += rho*theta * wt;
+        if (nt > 0) tracers(idWV,HS+k,HS+j,HS+i,iens) += rho_v * wt;
+      }
+    }
+    h.dycore.convert_dynamics_to_coupler(c, state, tracers);
+    return 0;
+  } catch (std::string &s) { std::cerr << "ref_init_thermal: " << s << std::endl; return 1; } catch (...) { return 1; }
+}
+
 // Wall-clock seconds for `nsteps` raw reference time steps (CPU baseline timing).
 double ref_time_steps_raw(void *hv, int nsteps) {
   Handle &h = *(Handle*)hv;

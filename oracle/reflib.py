@@ -71,6 +71,10 @@ def load(ord=5, omp=False):
     lib.ref_compute_gcm_forcing_tendencies.argtypes = [C.c_void_p]
     lib.ref_apply_gcm_forcing_tendencies.argtypes = [C.c_void_p]
     lib.ref_perturb_temperature.argtypes = [C.c_void_p, C.POINTER(C.c_int), C.c_double]
+    lib.ref_gll9.argtypes = [_dp, _dp]
+    lib.ref_gll9.restype = None
+    lib.ref_init_supercell.argtypes = [C.c_void_p]
+    lib.ref_init_thermal.argtypes = [C.c_void_p]
     lib.ref_shutdown.restype = None
     atexit.register(lib.ref_shutdown)
     _libs[key] = lib
@@ -173,6 +177,18 @@ class RefDycore:
         a = np.ascontiguousarray(ids, dtype=np.int32)
         assert a.size == self.nens
         assert self.lib.ref_perturb_temperature(self.h, a.ctypes.data_as(C.POINTER(C.c_int)), float(magnitude)) == 0
+
+    # ---- idealized initial states (Dycore.h:1017-1086 thermal, :1096-1276 supercell) ----
+    def gll9(self):
+        p, w = np.empty(9), np.empty(9)
+        self.lib.ref_gll9(_p(p), _p(w))
+        return p, w
+
+    def init_supercell(self):
+        assert self.lib.ref_init_supercell(self.h) == 0
+
+    def init_thermal(self):
+        assert self.lib.ref_init_thermal(self.h) == 0
 
     # ---- tables ----
     def tables(self):

@@ -428,6 +428,160 @@ __global__ void __launch_bounds__(256) k_fp64_peak(int iters, double seed, doubl
   if (s == 12345.6789) sink[0] = s;
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// Idealized initial states of Dycore::init (Dycore.h:985-1091): supercell sounding (init_supercell, :1096-1276, point
+// functions :774-830) and rising thermal (:1017-1086, point functions :742-769), each followed by
+// convert_dynamics_to_coupler (:1281-1331). Init-time kernels: a column kernel (hydrostatic integration up the column:
+// one thread per member resp. per (level, member)) and a cell kernel (9x9x9 Gauss-Legendre-Lobatto cell averages, in
+// the reference's summation order). Every member integrates its OWN column (the reference's cell-average kernel
+// overwrites all members from each thread, Dycore.h:1228-1231 -- the same thing whenever members share a grid).
+// ---------------------------------------------------------------------------------------------------------------
+__constant__ double c_gll9_pts[9] = AWFL_GLL9_PTS_INIT;
+__constant__ double c_gll9_wts[9] = AWFL_GLL9_WTS_INIT;
+
+struct InitArgs {
+  const double *zint;            // (nz+1,nens)
+  double *pg, *vapg;             // (nz,9,nens): pressure / vapour density at the GLL points of every cell
+  double *hy_dens, *hy_pres;     // (nz,nens)
+  double xlen, ylen, cp_d, p0;
+};
+
+__device__ __forceinline__ double sc_temperature(double z, double z_top) {
+  const double z_0 = 0, z_trop = 12000, T_0 = 300, T_trop = 213, T_top = 213;
+  if (z <= z_trop) { const double lapse = -(T_trop - T_0) / (z_trop - z_0); return T_0 - lapse * (z - z_0); }
+  const double lapse = -(T_top - T_trop) / (z_top - z_trop);
+  return T_trop - lapse * (z - z_trop);
+}
+__device__ __forceinline__ double sc_pressure_dry(double z, double z_top, double R_d, double grav) {
+  const double z_0 = 0, z_trop = 12000, T_0 = 300, T_trop = 213, p_0 = 100000;
+  const double lapse = -(T_trop - T_0) / (z_trop - z_0);
+  if (z <= z_trop) return p_0 * pow(sc_temperature(z, z_top) / T_0, grav / (R_d * lapse));
+  const double p_trop = p_0 * pow(T_trop / T_0, grav / (R_d * lapse));
+  return p_trop * exp(-grav * (z - z_trop) / (R_d * T_trop));      // T_top == T_trop: the isothermal branch (:805-807)
+}
+__device__ __forceinline__ double sc_qv(double z, double z_top, double R_d, double grav, double &temp) {
+  temp = sc_temperature(z, z_top);
+  const double qvs = 380 / sc_pressure_dry(z, z_top, R_d, grav) * exp(17.27 * (temp - 273) / (temp - 36));
+  double relhum = z <= 12000.0 ? 1.0 - 0.75 * pow(z / 12000.0, 1.25) : 0.25;
+  if (relhum * qvs > 0.014) relhum = 0.014 / qvs;
+  return fmin(0.014, qvs * relhum);       // like std::min(0.014, x): a NaN x (height rounded below zero) gives 0.014
+}
+
+__global__ void __launch_bounds__(64) k_init_supercell_column(const Geom g, const Phys ph, const InitArgs a) {
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= g.nens) return;
+  const double z_top = a.zint[(long)g.nz * g.nens + e];
+  double p = 100000.0;
+  for (int k = 0; k < g.nz; k++) {
+    const double z0 = a.zint[(long)k * g.nens + e], z1 = a.zint[(long)(k + 1) * g.nens + e];
+    const double dz = z1 - z0, zmid = 0.5 * (z0 + z1);
+    a.pg[((long)k * 9) * g.nens + e] = p;
+    for (int kk = 0; kk < 8; kk++) {
+      const double b = zmid + c_gll9_pts[kk] * dz, t = zmid + c_gll9_pts[kk + 1] * dz, m = 0.5 * (b + t);
+      const double sub = dz * (c_gll9_pts[kk + 1] - c_gll9_pts[kk]);
+      double tot = 0;
+      for (int q = 0; q < 9; q++) {
+        double temp;
+        const double qv = sc_qv(m + sub * c_gll9_pts[q], z_top, ph.R_d, ph.grav, temp);
+        tot += (-(1 + qv) * ph.grav / (ph.R_d + qv * ph.R_v) / temp) * c_gll9_wts[q];
+      }
+      tot *= sub;
+      p = p * exp(tot);
+      a.pg[((long)k * 9 + kk + 1) * g.nens + e] = p;
+    }
+    double press_tot = 0, dens_tot = 0;
+    for (int kk = 0; kk < 9; kk++) {
+      double temp;
+      const double qv = sc_qv(zmid + c_gll9_pts[kk] * dz, z_top, ph.R_d, ph.grav, temp);
+      const double press = a.pg[((long)k * 9 + kk) * g.nens + e];
+      const double dens_dry = press / (ph.R_d + qv * ph.R_v) / temp, dens_vap = qv * dens_dry;
+      a.vapg[((long)k * 9 + kk) * g.nens + e] = dens_vap;
+      press_tot += press * c_gll9_wts[kk];
+      dens_tot += (dens_dry + dens_vap) * c_gll9_wts[kk];
+    }
+    a.hy_dens[(long)k * g.nens + e] = dens_tot;
+    a.hy_pres[(long)k * g.nens + e] = press_tot;
+  }
+}
+
+__global__ void __launch_bounds__(128) k_init_thermal_column(const Geom g, const Phys ph, const InitArgs a) {
+  const int e = blockIdx.x * blockDim.x + threadIdx.x, k = blockIdx.y;
+  if (e >= g.nens) return;
+  const double z0 = a.zint[(long)k * g.nens + e], z1 = a.zint[(long)(k + 1) * g.nens + e];
+  const double dz = z1 - z0, zmid = 0.5 * (z0 + z1);
+  double hd = 0, hp = 0;
+  for (int kk = 0; kk < 9; kk++) {
+    const double z = zmid + c_gll9_pts[kk] * dz;
+    const double exner = 1.0 - ph.grav * z / (a.cp_d * 300.0);               // hydro_const_theta, Dycore.h:742-752
+    const double p = a.p0 * pow(exner, a.cp_d / ph.R_d);
+    const double rt = pow(p / ph.C0, 1.0 / ph.gamma);
+    const double hr = rt / 300.0;
+    hd += hr * c_gll9_wts[kk];
+    hp += ph.C0 * pow(hr * 300.0, ph.gamma) * c_gll9_wts[kk];
+  }
+  a.hy_dens[(long)k * g.nens + e] = hd;
+  a.hy_pres[(long)k * g.nens + e] = hp;
+}
+
+// spec 0: thermal, 1: supercell. One thread per cell; writes the coupler fields.
+__global__ void __launch_bounds__(128)
+k_init_cells(const Geom g, const Phys ph, const InitArgs a, const FieldPtrs fp, int idWV, const unsigned char *adds_mass, int spec,
+             const RowMap rm) {
+  long cell; int k, j, i, e;
+  if (!row_coords(g, rm, cell, k, j, i, e)) return;
+  const double z0 = a.zint[(long)k * g.nens + e], z1 = a.zint[(long)(k + 1) * g.nens + e];
+  const double dz = z1 - z0, zmid = 0.5 * (z0 + z1);
+  const double hd = a.hy_dens[(long)k * g.nens + e], hp = a.hy_pres[(long)k * g.nens + e];
+  double rho, ru = 0, rv = 0, rw = 0, rt, wv = 0;
+  if (spec == 1) {
+    rho = hd;
+    rt = pow(hp / ph.C0, 1.0 / ph.gamma);
+    for (int kk = 0; kk < 9; kk++) {
+      const double zloc = zmid + c_gll9_pts[kk] * dz;
+      const double uvel = zloc < 5000.0 ? 30.0 * (zloc / 5000.0) - 15.0 : 30.0 - 15.0;
+      const double dens_vap = a.vapg[((long)k * 9 + kk) * g.nens + e];
+      for (int jj = 0; jj < 9; jj++)
+        for (int ii = 0; ii < 9; ii++) {
+          const double factor = c_gll9_wts[ii] * c_gll9_wts[jj] * c_gll9_wts[kk];
+          ru += rho * uvel * factor;
+          wv += dens_vap * factor;
+        }
+    }
+  } else {
+    const double dxx = g.dx, dyy = g.dy;
+    const double ht = pow(hp / ph.C0, 1.0 / ph.gamma) / hd;
+    rho = 0; rt = 0;
+    for (int kk = 0; kk < 9; kk++)
+      for (int jj = 0; jj < 9; jj++)
+        for (int ii = 0; ii < 9; ii++) {
+          const double x = (i + 0.5) * dxx + c_gll9_pts[ii] * dxx;
+          double y = (j + 0.5) * dyy + c_gll9_pts[jj] * dyy;
+          if (g.sim2d) y = a.ylen / 2;
+          const double z = zmid + c_gll9_pts[kk] * dz;
+          // sample_ellipse_cosine(2, x,y,z, xlen/2, ylen/2, 2000, 2000,2000,2000), Dycore.h:757-769
+          const double xr = (x - a.xlen / 2) / 2000., yr = (y - a.ylen / 2) / 2000., zr = (z - 2000.) / 2000.;
+          const double dist = sqrt(xr * xr + yr * yr + zr * zr) * M_PI / 2.;
+          double bump = 0.;
+          if (dist <= M_PI / 2.) { const double cd = cos(dist); bump = 2.0 * (cd * cd); }
+          const double theta = ht + bump;
+          const double wt = c_gll9_wts[ii] * c_gll9_wts[jj] * c_gll9_wts[kk];
+          rho += hd * wt;
+          rt += hd * theta * wt;
+        }
+  }
+  // convert_dynamics_to_coupler, Dycore.h:1313-1330
+  const double theta = rt / rho;
+  const double press = ph.C0 * pow(rho * theta, ph.gamma);
+  double rho_d = rho;
+  for (int t = 0; t < g.nt; t++) {
+    const double x = t == idWV ? wv : 0.0;
+    if (adds_mass[t]) rho_d -= x;
+    fp.tr[t][cell] = x;
+  }
+  fp.f[0][cell] = rho_d; fp.f[1][cell] = ru / rho; fp.f[2][cell] = rv / rho; fp.f[3][cell] = rw / rho;
+  fp.f[4][cell] = press / (rho_d * ph.R_d + wv * ph.R_v);
+}
+
 }  // namespace awfl
 
 // =================================================================================================================
@@ -1143,6 +1297,30 @@ int awfl_declare_hydrostatic(awfl_handle *h, const awfl_fields *f, const awfl_gc
   h->launches++;
   CK(cudaGetLastError());
   CK(cudaStreamSynchronize(h->stream));
+  return 0;
+}
+
+int awfl_init_idealized(awfl_handle *h, const awfl_fields *f, const double *zint, int data_spec) {
+  if (data_spec != 0 && data_spec != 1) return fail(h, "awfl_init_idealized: data_spec must be 0 (thermal) or 1 (supercell)");
+  if (!zint) return fail(h, "awfl_init_idealized: vertical_interface_height is required");
+  const Geom &g = h->g;
+  FieldPtrs fp;
+  if (make_field_ptrs(h, f, fp)) return 1;
+  // init-time scratch (not a time-step path): pressure / vapour at the 9 GLL points of every cell + two columns
+  const size_t n2 = (size_t)g.nz * g.nens;
+  double *scratch = nullptr;
+  CK(cudaMalloc((void **)&scratch, sizeof(double) * (18 + 2) * n2));
+  InitArgs a;
+  a.zint = zint; a.pg = scratch; a.vapg = scratch + 9 * n2; a.hy_dens = scratch + 18 * n2; a.hy_pres = scratch + 19 * n2;
+  a.xlen = h->cfg.xlen; a.ylen = h->cfg.ylen; a.cp_d = h->cfg.cp_d; a.p0 = h->cfg.p0;
+  if (data_spec == 1) k_init_supercell_column<<<(unsigned)(g.nens + 63) / 64, 64, 0, h->stream>>>(g, h->ph, a);
+  else k_init_thermal_column<<<dim3((unsigned)(g.nens + 127) / 128, (unsigned)g.nz), 128, 0, h->stream>>>(g, h->ph, a);
+  const RowMap rm = row_map(g, 128);
+  k_init_cells<<<row_blocks(g, rm), 128, 0, h->stream>>>(g, h->ph, a, fp, h->cfg.idWV, h->adds_mass_d, data_spec, rm);
+  h->launches += 2;
+  cudaError_t e1 = cudaGetLastError(), e2 = cudaStreamSynchronize(h->stream);
+  cudaFree(scratch);
+  if (e1 != cudaSuccess || e2 != cudaSuccess) return fail(h, std::string("awfl_init_idealized: ") + cudaGetErrorString(e1 != cudaSuccess ? e1 : e2));
   return 0;
 }
 

@@ -90,6 +90,26 @@ class Dycore:
         if not dm.entry_exists("hy_dens_cells"):
             dm.register_and_allocate("hy_dens_cells", "", (nz, nens))
             dm.register_and_allocate("hy_pressure_cells", "", (nz, nens))
+        # idealized initial data, Dycore.h:985-1091: chosen by "initData" of the standalone driver's YAML file
+        if coupler.option_exists("standalone_input_file"):
+            import yaml
+            with open(coupler.get_option("standalone_input_file")) as fh:
+                config = yaml.safe_load(fh)
+            data = str(config.get("initData"))
+            if data in ("thermal", "supercell"):
+                self.init_idealized_state_and_tracers(coupler, data)
+            elif data != "external":
+                endrun("ERROR: Invalid data_spec")                                     # Dycore.h:1001
+
+    def init_idealized_state_and_tracers(self, coupler, data_spec):
+        """The DATA_SPEC_THERMAL / DATA_SPEC_SUPERCELL branches of Dycore::init (Dycore.h:1007-1088; init_supercell
+        :1096-1276): overwrite the coupler fields with the idealized state."""
+        spec = {"thermal": 0, "supercell": 1}.get(data_spec)
+        if spec is None:
+            endrun("ERROR: Invalid data_spec")
+        f, keep = self._fields(coupler)
+        zint = coupler.get_data_manager_device_readonly().get("vertical_interface_height", 2, readonly=True)
+        self._rc(self.lib.awfl_init_idealized(self.h, C.byref(f), zint.data_ptr(), spec), "awfl_init_idealized")
 
     def _view(self, ptr, shape):
         """Non-owning torch view of handle-owned device memory (DataManager `get` returns non-owning views too)."""

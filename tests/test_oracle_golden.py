@@ -23,7 +23,7 @@ import helpers as H
 import make_golden as MG
 from oracle import oraclelib, reflib
 
-GOLDEN = sorted(p for p in glob.glob(os.path.join(ROOT, "tests", "golden", "*.npz")) if not os.path.basename(p).startswith("modules_"))
+GOLDEN = sorted(p for p in glob.glob(os.path.join(ROOT, "tests", "golden", "*.npz")) if not os.path.basename(p).startswith(("modules_", "init_")))
 TOL = 1e-13
 
 

@@ -148,6 +148,23 @@ def mpd(x):
     return float(x).hex()
 
 
+def gll(n):
+    """Gauss-Legendre-Lobatto nodes and weights on [-1/2, 1/2] (weights sum to 1): nodes = +-1 and the roots of P'_{n-1},
+    weights 2/(n(n-1) P_{n-1}(x)^2), both halved. The reference tabulates the same numbers as decimal literals
+    (TransformMatrices.h get_gll_points / get_gll_weights, SArray<FP,1,9> overloads); tests check equality."""
+    import mpmath
+    import numpy as np
+    mpmath.mp.dps = 60
+    c = np.zeros(n)
+    c[n - 1] = 1
+    guess = np.sort(np.polynomial.legendre.legroots(np.polynomial.legendre.legder(c)))
+    P = lambda x: mpmath.legendre(n - 1, x)
+    xs = [mpmath.mpf(-1)] + [mpmath.findroot(lambda x: mpmath.diff(P, x), mpmath.mpf(float(v))) for v in guess] + [mpmath.mpf(1)]
+    xs = [mpmath.mpf(0) if abs(x) < 1e-40 else x for x in xs]
+    ws = [2 / (n * (n - 1) * P(x) ** 2) for x in xs]
+    return [x / 2 for x in xs], [w / 2 for w in ws]
+
+
 def dbl(fr):
     """nearest double of a Fraction as a C hex-float literal (exact, no decimal round trip)"""
     x = fr.numerator / fr.denominator if isinstance(fr, F) else float(fr)   # int/int is correctly rounded
@@ -168,6 +185,11 @@ def emit(guard):
     w("#else")
     w("#define AWFL_TBL_QUAL static const")
     w("#endif")
+    pts, wts = gll(9)
+    w("")
+    w("// ---- 9-point Gauss-Legendre-Lobatto rule on [-1/2,1/2] (idealized initial states, Dycore.h:1027-1031, :1106-1109) ----")
+    w("#define AWFL_GLL9_PTS_INIT {%s}" % ", ".join(float(x).hex() for x in pts))
+    w("#define AWFL_GLL9_WTS_INIT {%s}" % ", ".join(float(x).hex() for x in wts))
     for o in ORDS:
         m = (o + 1) // 2
         S = sten_to_coefs(o)

@@ -59,6 +59,11 @@ int pamm_compute_gcm_forcing_tendencies(pamm_workspace *w, const pamm_crm_fields
 int pamm_apply_gcm_forcing_tendencies(pamm_workspace *w, const pamm_crm_fields *crm, const pamm_gcm_columns *gcm,
                                       const pamm_forcing_tend *tend, const double *dz, double crm_dt, double gcm_physics_dt);
 
+/* modules::broadcast_initial_gcm_column (pam_core/modules/broadcast_initial_gcm_column.h:7-41): fill density_dry,
+ * uvel, vvel, wvel, temp, water_vapor with the GCM columns gcm_density_dry, gcm_uvel, gcm_vvel, gcm_wvel, gcm_temp,
+ * gcm_water_vapor. Both arguments: HOST arrays of 6 device pointers in that order. */
+int pamm_broadcast_initial_gcm_column(pamm_workspace *w, const double *const *gcm_columns, double *const *fields);
+
 /* modules::perturb_temperature (pam_core/modules/perturb_temperature.h:10-63): add a random perturbation of at most
  * +-magnitude*(num_levels-k)/num_levels K (num_levels = nz/4) to temp in the lowest num_levels levels, then rescale
  * each perturbed level to its original horizontal mean. The random numbers are the reference's: yakl::Random (the

@@ -271,6 +271,18 @@ __global__ void __launch_bounds__(128) k_perturb_temperature(const Dims d, doubl
   }
 }
 
+// modules::broadcast_initial_gcm_column (pam_core/modules/broadcast_initial_gcm_column.h:7-41): every cell of a level
+// takes the GCM column's value. One thread = (level, member) writing its ny*nx cells of the six fields.
+struct BroadcastArgs { const double *col[6]; double *fld[6]; };
+__global__ void __launch_bounds__(128) k_broadcast_column(const Dims d, const BroadcastArgs a) {
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  const int k = blockIdx.y, f = blockIdx.z;
+  if (e >= d.nens) return;
+  const double v = a.col[f][(long)k * d.nens + e];
+  double *x = a.fld[f] + (long)k * d.ny * d.nx * d.nens + e;
+  for (int c = 0; c < d.ny * d.nx; c++) x[(long)c * d.nens] = v;
+}
+
 }  // namespace
 
 // =================================================================================================================
@@ -340,6 +352,16 @@ int pamm_apply_gcm_forcing_tendencies(pamm_workspace *w, const pamm_crm_fields *
   k_fill_holes_global<<<dim3((unsigned)(w->nens + 127) / 128, 3), 128, 0, w->stream>>>(d, crm->water_vapor, crm->cloud_water, crm->ice, dz,
                                                                                        w->scratch);
   w->launches += 2;
+  PCK(cudaGetLastError());
+  return 0;
+}
+
+int pamm_broadcast_initial_gcm_column(pamm_workspace *w, const double *const *gcm_columns, double *const *fields) {
+  BroadcastArgs a;
+  for (int f = 0; f < 6; f++) { a.col[f] = gcm_columns[f]; a.fld[f] = fields[f]; }
+  const Dims d{w->nz, w->ny, w->nx, w->nens};
+  k_broadcast_column<<<dim3((unsigned)(w->nens + 127) / 128, (unsigned)w->nz, 6), 128, 0, w->stream>>>(d, a);
+  w->launches++;
   PCK(cudaGetLastError());
   return 0;
 }

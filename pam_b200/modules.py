@@ -51,6 +51,7 @@ def _bind(lib):
     lib.pamm_compute_gcm_forcing_tendencies.argtypes = [C.c_void_p, C.POINTER(_Crm), C.POINTER(_Gcm), C.POINTER(_Tend), C.c_double]
     lib.pamm_apply_gcm_forcing_tendencies.argtypes = [C.c_void_p, C.POINTER(_Crm), C.POINTER(_Gcm), C.POINTER(_Tend), C.c_void_p,
                                                       C.c_double, C.c_double]
+    lib.pamm_broadcast_initial_gcm_column.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p)]
     lib.pamm_perturb_temperature.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_double]
     _bound = True
 
@@ -140,6 +141,17 @@ def apply_gcm_forcing_tendencies(coupler):
     w.rc(w.lib.pamm_apply_gcm_forcing_tendencies(w.h, C.byref(crm), C.byref(gcm), C.byref(tend), dz.data_ptr(),
                                                  float(coupler.get_option("crm_dt")), float(coupler.get_option("gcm_physics_dt"))),
          "pamm_apply_gcm_forcing_tendencies")
+
+
+def broadcast_initial_gcm_column(coupler):
+    """modules::broadcast_initial_gcm_column (pam_core/modules/broadcast_initial_gcm_column.h:7-41)."""
+    w = _ws(coupler)
+    dm = coupler.get_data_manager_device_readwrite()
+    cols = ("gcm_density_dry", "gcm_uvel", "gcm_vvel", "gcm_wvel", "gcm_temp", "gcm_water_vapor")
+    flds = ("density_dry", "uvel", "vvel", "wvel", "temp", "water_vapor")
+    cp = (C.c_void_p * 6)(*[dm.get(n, 2, readonly=True).data_ptr() for n in cols])
+    fp = (C.c_void_p * 6)(*[dm.get(n, 4).data_ptr() for n in flds])
+    w.rc(w.lib.pamm_broadcast_initial_gcm_column(w.h, cp, fp), "pamm_broadcast_initial_gcm_column")
 
 
 def perturb_temperature(coupler, ids, magnitude=0.1):

@@ -304,11 +304,19 @@ def main():
     elif dom.startswith("tracer_") and dom != "tracer_upd":
         fl = (roofline.recon_flops(w["ord"])[0] + 4) * ncell * nt
         by = 8 * 4 * ncell * nt
+    elif dom == "tracer_upd" and w["ny"] == 1:
+        fl, by = 60.0 * ncell * nt, 8 * 5 * ncell * nt       # fused 2-D FCT + update: reads 2 fluxes + 2 states, writes 1 state
     else:
         fl, by = 40.0 * ncell * nt, 8 * 12 * ncell * nt
+    traffic = None
+    try:
+        tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+        traffic = tj.get(args.workload, {}).get(dom, {}).get("bytes") if w["ord"] == 5 else None
+    except Exception:
+        pass
     dur = dom_ms / max(dom_n, 1) * 1e-3
     roof = {"bound": "fp64", "kernel": dom, "achieved": fl / dur / 1e12, "peak": fp64_peak, "unit": "TFLOP/s",
-            "frac": fl / dur / 1e12 / fp64_peak, "traffic": None,
+            "frac": fl / dur / 1e12 / fp64_peak, "traffic": traffic,
             "peak_source": "DFMA-chain microbenchmark run in this process (awfl_measure_fp64_peak); FP64 peak is not in MEASURED_PEAKS.json",
             "flops_per_launch": fl, "avg_launch_ms": dur * 1e3, "share_of_step": dom_ms / tot_ms,
             "hbm": {"achieved": by / dur / 1e9, "peak": hbm_peak, "unit": "GB/s", "frac": by / dur / 1e9 / hbm_peak,

@@ -105,6 +105,23 @@ class Dycore {
     if (!dm.entry_exists("hy_pressure_cells")) dm.template register_and_allocate<real>("hy_pressure_cells", "", {nz, nens});
     check(awfl_export_tables(h_, dm.template get<real, 2>("variable_gravity").data(), dm.template get<real, 4>("vert_sten_to_coefs").data(),
                              dm.template get<real, 5>("vert_weno_recon_lower").data()), "awfl_export_tables");
+    // idealized initial data, Dycore.h:985-1091: "initData" of the standalone driver's YAML file (the reference parses it
+    // with yaml-cpp under PAM_STANDALONE; one "key : value" line is all that is read, so it is scanned for here)
+    if (coupler.option_exists("standalone_input_file")) {
+      const std::string data = yaml_scalar(coupler.template get_option<std::string>("standalone_input_file"), "initData");
+      if (data == "thermal") init_idealized_state_and_tracers(coupler, 0);
+      else if (data == "supercell") init_idealized_state_and_tracers(coupler, 1);
+      else if (data != "external") endrun("ERROR: Invalid data_spec");                       // Dycore.h:1001
+    }
+  }
+
+  // The DATA_SPEC_THERMAL (0) / DATA_SPEC_SUPERCELL (1) branches of Dycore::init (Dycore.h:1007-1088; init_supercell
+  // :1096-1276): overwrite the coupler fields with the idealized state.
+  template <class Coupler>
+  void init_idealized_state_and_tracers(Coupler &coupler, int data_spec) {
+    Fields<Coupler> f(coupler, nt_);
+    auto &dm = coupler.get_data_manager_device_readwrite();
+    check(awfl_init_idealized(h_, &f.f, dm.template get<real const, 2>("vertical_interface_height").data(), data_spec), "awfl_init_idealized");
   }
 
   // Dycore::timeStep (Dycore.h:107-255)
@@ -179,6 +196,29 @@ class Dycore {
       f.tracers = tr.data();
     }
   };
+
+  // value of a top-level "key : value" line of a YAML file ("" if absent); comments and quotes stripped
+  static std::string yaml_scalar(const std::string &path, const std::string &key) {
+    std::FILE *f = std::fopen(path.c_str(), "r");
+    if (!f) awfl_b200_detail::endrun("ERROR: could not open " + path);
+    char line[1024];
+    std::string out;
+    while (std::fgets(line, sizeof(line), f)) {
+      std::string l(line);
+      const size_t hash = l.find('#');
+      if (hash != std::string::npos) l.erase(hash);
+      const size_t colon = l.find(':');
+      if (colon == std::string::npos) continue;
+      auto trim = [](std::string x) {
+        const char *ws = " \t\r\n\"'";
+        const size_t b = x.find_first_not_of(ws), e = x.find_last_not_of(ws);
+        return b == std::string::npos ? std::string() : x.substr(b, e - b + 1);
+      };
+      if (trim(l.substr(0, colon)) == key) { out = trim(l.substr(colon + 1)); break; }
+    }
+    std::fclose(f);
+    return out;
+  }
 
   template <class T, class Coupler>
   static void set_default(Coupler &c, const char *key, T v) {

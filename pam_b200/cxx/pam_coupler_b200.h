@@ -118,22 +118,26 @@ class DataManager {
 class Options {
  public:
   template <class T> void set_option(std::string key, T v) {
-    Val x; x.type = typeid(T).hash_code(); std::memset(x.raw, 0, sizeof(x.raw)); std::memcpy(x.raw, &v, sizeof(T));
-    static_assert(sizeof(T) <= 16, "option type too large");
+    Val x; x.type = typeid(T).hash_code(); std::memset(x.raw, 0, sizeof(x.raw));
+    if constexpr (std::is_same<T, std::string>::value) { x.str = v; }                // Options.h stores std::string too
+    else {
+      static_assert(sizeof(T) <= 16, "option type too large");
+      std::memcpy(x.raw, &v, sizeof(T));
+    }
     vals_[key] = x;
   }
   template <class T> T get_option(std::string key) const {
     auto it = vals_.find(key);
     if (it == vals_.end()) endrun("ERROR: option key does not exist: " + key);       // Options.h:84-87
     if (it->second.type != typeid(T).hash_code()) endrun("ERROR: Requesting option with the wrong type: " + key);
-    T v; std::memcpy(&v, it->second.raw, sizeof(T));
-    return v;
+    if constexpr (std::is_same<T, std::string>::value) { return it->second.str; }
+    else { T v; std::memcpy(&v, it->second.raw, sizeof(T)); return v; }
   }
   bool option_exists(std::string key) const { return vals_.count(key) > 0; }
   void delete_option(std::string key) { vals_.erase(key); }
 
  private:
-  struct Val { size_t type; unsigned char raw[16]; };
+  struct Val { size_t type; unsigned char raw[16]; std::string str; };
   std::map<std::string, Val> vals_;
 };
 
@@ -166,7 +170,8 @@ class PamCoupler {
     dm_.register_and_allocate<real>("vertical_interface_height", "", {nz + 1, nens});
     dm_.register_and_allocate<real>("vertical_cell_dz", "", {nz, nens});
     dm_.register_and_allocate<real>("vertical_midpoint_height", "", {nz, nens});
-    for (const char *n : {"gcm_density_dry", "gcm_uvel", "gcm_vvel", "gcm_wvel", "gcm_temp", "gcm_water_vapor", "gcm_cloud_water", "gcm_cloud_ice"})
+    for (const char *n : {"gcm_density_dry", "gcm_uvel", "gcm_vvel", "gcm_wvel", "gcm_temp", "gcm_water_vapor", "gcm_cloud_water", "gcm_cloud_ice",
+                          "gcm_num_liq", "gcm_num_ice", "gcm_num_rain"})   // pam_coupler.h:268-281
       dm_.register_and_allocate<real>(n, "", {nz, nens});
   }
   // pam_coupler.h:184-202: zint is a HOST array of nz+1 interface heights, the same for every ensemble member

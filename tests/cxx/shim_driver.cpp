@@ -10,6 +10,7 @@
 #include <vector>
 
 #include "pam_coupler_b200.h"
+#include "modules_b200.h"
 
 using pam_b200::PamCoupler;
 
@@ -41,7 +42,7 @@ static int selftest() {
 
 static void rd(FILE *f, void *p, size_t n) { if (std::fread(p, 1, n, f) != n) { std::printf("short read\n"); std::exit(2); } }
 
-static int run(const char *in, const char *out, int nsteps) {
+static int run(const char *in, const char *out, int nsteps, bool mmf) {
   FILE *f = std::fopen(in, "rb");
   if (!f) { std::printf("cannot open %s\n", in); return 2; }
   int hdr[6];   // nz ny nx nens nt use_default_consts
@@ -78,7 +79,28 @@ static int run(const char *in, const char *out, int nsteps) {
   std::fclose(f);
   dycore.declare_current_profile_as_hydrostatic(coupler);
   const double dt_cfl = dycore.compute_time_step(coupler);
-  for (int s = 0; s < nsteps; s++) coupler.run_module("dycore", [&](PamCoupler &c) { dycore.timeStep(c); });   // driver.cpp:248
+  if (mmf) {
+    // MMF-style loop (driver.cpp:239-250) through modules_b200.h. GCM columns by a rule the Python test repeats:
+    // 0.9 x the value of cell (k, j=0, i=0) of the matching CRM field.
+    coupler.set_option<real>("gcm_physics_dt", 20.0);
+    const char *gn[10] = {"gcm_density_dry", "gcm_uvel", "gcm_vvel", "gcm_temp", "gcm_water_vapor", "gcm_cloud_water", "gcm_cloud_ice",
+                          "gcm_num_liq", "gcm_num_ice", "gcm_num_rain"};
+    const char *cn[10] = {"density_dry", "uvel", "vvel", "temp", "water_vapor", "cloud_water", "ice", "cloud_water_num", "ice_num", "rain_num"};
+    std::vector<double> col((size_t)nz * nens);
+    for (int v = 0; v < 10; v++) {
+      dm.read<real>(cn[v], buf.data());
+      for (int k = 0; k < nz; k++) for (int e = 0; e < nens; e++) col[(size_t)k * nens + e] = 0.9 * buf[(size_t)k * ny * nx * nens + e];
+      dm.write<real>(gn[v], col.data());
+    }
+    modules::compute_gcm_forcing_tendencies(coupler);
+    for (int s = 0; s < nsteps; s++) {
+      coupler.run_module("apply_gcm_forcing_tendencies", modules::apply_gcm_forcing_tendencies<PamCoupler>);
+      coupler.run_module("dycore", [&](PamCoupler &c) { dycore.timeStep(c); });
+      coupler.run_module("sponge_layer", modules::sponge_layer<PamCoupler>);
+    }
+  } else {
+    for (int s = 0; s < nsteps; s++) coupler.run_module("dycore", [&](PamCoupler &c) { dycore.timeStep(c); });   // driver.cpp:248
+  }
   std::vector<real> mass = dycore.compute_mass(coupler);
   FILE *g = std::fopen(out, "wb");
   std::fwrite(&dt_cfl, sizeof(double), 1, g);
@@ -97,8 +119,8 @@ static int run(const char *in, const char *out, int nsteps) {
 int main(int argc, char **argv) {
   try {
     if (argc >= 2 && !std::strcmp(argv[1], "selftest")) return selftest();
-    if (argc >= 5 && !std::strcmp(argv[1], "run")) return run(argv[2], argv[3], std::atoi(argv[4]));
+    if (argc >= 5 && !std::strcmp(argv[1], "run")) return run(argv[2], argv[3], std::atoi(argv[4]), argc >= 6 && !std::strcmp(argv[5], "mmf"));
   } catch (std::string &s) { std::printf("endrun: %s\n", s.c_str()); return 3; }
-  std::printf("usage: shim_driver selftest | run IN OUT NSTEPS\n");
+  std::printf("usage: shim_driver selftest | run IN OUT NSTEPS [mmf]\n");
   return 64;
 }

@@ -276,7 +276,7 @@ def main():
         fb = 8 * ncell * len(names)
         e2e = {"value": float(eu.item()) / float(te.item()), "unit": "cell-updates/s", "h2d_bytes_per_step": fb * world,
                "d2h_bytes_per_step": fb * world, "steps": nst,
-               "host_slabs": args.host_slabs or 4,
+               "host_slabs": d.host_slabs(),
                "note": "awfl_time_step_host: pinned host fields -> device, Dycore::timeStep, device -> host, every step; the ensemble "
                        "is pipelined in member slabs so that copies of one slab overlap the kernels of another"}
 

@@ -76,9 +76,11 @@ int awfl_time_step(awfl_handle *h, const awfl_fields *f, double crm_dt, int ncyc
 int awfl_time_step_host(awfl_handle *h, double *const *host_fields, double crm_dt, int ncycles_override, int *ncycles_out);
 
 /* Number of member slabs awfl_time_step_host pipelines (copy of one slab overlaps the kernels of another; CRMs are
- * independent, so results do not depend on it). Default 4 (or the environment variable AWFL_HOST_SLABS); 1 = copy
- * everything, step, copy everything back. */
+ * independent, so results do not depend on it). 0 (default, or the environment variable AWFL_HOST_SLABS) = chosen from
+ * the grid so that the slabs in flight fill the GPU once; 1 = copy everything, step, copy everything back.
+ * awfl_host_slabs returns the count the next call will use. */
 int awfl_set_host_slabs(awfl_handle *h, int nslabs);
+int awfl_host_slabs(const awfl_handle *h);
 
 /* awfl_time_step_host starts its slabs with a predicted sub-cycle count (the previous call's) before the CFL dt of the
  * whole ensemble is known and redoes the step, un-overlapped, when the prediction was wrong: how often that happened. */

@@ -615,6 +615,8 @@ struct awfl_handle {
   unsigned char *positive_d, *adds_mass_d;
   std::vector<unsigned char> positive_h, adds_mass_h;
   double **trptr_d;      // device array of tracer field pointers
+  double **trptr_out_d;  // the same for the result staging of the host-buffer entry point
+  double *stage_out;     // result staging of the host-buffer entry point (the staged inputs stay intact beside it)
   // optional per-kernel-class CUDA-event timing (awfl_profile_begin/end)
   bool prof;
   std::vector<cudaEvent_t> ev_pool;
@@ -624,8 +626,11 @@ struct awfl_handle {
   int host_last_ncycles;      // sub-cycle count derived by the previous awfl_time_step_host (0 = none yet): the prediction
   long host_mispredictions;   // calls whose prediction was wrong and were redone un-overlapped
   bool fused_fct;        // 2-D: fused FCT + tracer update kernel (AWFL_FUSED_FCT=0 selects the two-kernel path)
-  int host_slabs;        // member slabs of the host-buffer entry point (copy/compute overlap); 1 = no pipelining
+  int host_slabs;        // member slabs of the host-buffer entry point (copy/compute overlap); 1 = no pipelining, 0 = auto
   cudaStream_t s_in, s_out;              // copy streams of the host-buffer entry point
+  cudaStream_t s_cmp[4];                 // its compute streams: consecutive slabs alternate, so the tail of one slab's
+                                         // kernels (a partial wave of one-warp blocks) overlaps the head of the next slab's
+  int host_cstreams;                     // 1 = all slabs on the handle's stream, 2..4 = round robin over s_cmp
   std::vector<cudaEvent_t> slab_ev;      // 2 events per slab: inputs on the device / results ready on the device
   double *tmp_state;     // scratch for awfl_compute_tendencies
 };
@@ -975,13 +980,16 @@ int awfl_create(const awfl_config *cfg, awfl_handle **out) {
   ALLOC(h->mass_d, sizeof(double) * (nt + 2) * g.nens);
   ALLOC(h->positive_d, nt); ALLOC(h->adds_mass_d, nt);
   ALLOC(h->trptr_d, sizeof(double *) * nt);
-  h->stage_fields = nullptr; h->tmp_state = nullptr;
+  ALLOC(h->trptr_out_d, sizeof(double *) * nt);
+  h->stage_fields = nullptr; h->stage_out = nullptr; h->tmp_state = nullptr;
   { const char *ev = getenv("AWFL_FUSED_FCT"); h->fused_fct = !(ev && atoi(ev) == 0); }
   h->s_in = nullptr; h->s_out = nullptr; h->host_last_ncycles = 0; h->host_mispredictions = 0;
   {
-    // member slabs of awfl_time_step_host: 4 by default (measured on C2); AWFL_HOST_SLABS overrides
+    // member slabs of awfl_time_step_host: chosen from the grid by default (host_slab_count); AWFL_HOST_SLABS overrides
     const char *ev = getenv("AWFL_HOST_SLABS");
-    h->host_slabs = ev && atoi(ev) > 0 ? atoi(ev) : 4;
+    h->host_slabs = ev && atoi(ev) > 0 ? atoi(ev) : 0;
+    const char *ec = getenv("AWFL_HOST_CSTREAMS");
+    h->host_cstreams = ec && atoi(ec) > 0 ? atoi(ec) : 3;
   }
   if (cudaMallocHost((void **)&h->dt_min_h, sizeof(double)) != cudaSuccess) return bail("cudaMallocHost failed");
   cudaMemcpy(h->dz, cfg->dz_host, sizeof(double) * g.nz * g.nens, cudaMemcpyHostToDevice);
@@ -1009,8 +1017,8 @@ void awfl_destroy(awfl_handle *h) {
   for (int o = 0; o < 4; o++) if (g_cvtab_owner[o] == h) g_cvtab_owner[o] = nullptr;
   cudaFree(h->mult); cudaFree(h->dz); cudaFree(h->rdz); cudaFree(h->grav_var); cudaFree(h->vtab); cudaFree(h->vs2c); cudaFree(h->vwrl);
   cudaFree(h->pint); cudaFree(h->dt_min_d); cudaFree(h->mass_d); cudaFree(h->positive_d); cudaFree(h->adds_mass_d);
-  cudaFree(h->trptr_d); cudaFree(h->stage_fields); cudaFree(h->tmp_state);
-  if (h->s_in) { cudaStreamDestroy(h->s_in); cudaStreamDestroy(h->s_out); }
+  cudaFree(h->trptr_d); cudaFree(h->trptr_out_d); cudaFree(h->stage_fields); cudaFree(h->stage_out); cudaFree(h->tmp_state);
+  if (h->s_in) { cudaStreamDestroy(h->s_in); cudaStreamDestroy(h->s_out); for (int c = 0; c < 4; c++) cudaStreamDestroy(h->s_cmp[c]); }
   for (cudaEvent_t e : h->slab_ev) cudaEventDestroy(e);
   if (h->dt_min_h) cudaFreeHost(h->dt_min_h);
   for (cudaEvent_t e : h->ev_pool) cudaEventDestroy(e);
@@ -1149,62 +1157,131 @@ int awfl_time_step(awfl_handle *h, const awfl_fields *f, double crm_dt, int ncyc
 }
 
 int awfl_set_host_slabs(awfl_handle *h, int nslabs) {
-  if (nslabs < 1) return fail(h, "awfl_set_host_slabs: need at least one slab");
+  if (nslabs < 0) return fail(h, "awfl_set_host_slabs: need at least one slab (0 = choose from the grid)");
   h->host_slabs = nslabs;
   return 0;
 }
+
+// Slab count of the host-buffer entry point. The marching kernels run one-warp blocks whose run time hardly depends on
+// how full the SM is, so a slab costs a whole wave however few warps it brings: the slabs in flight (one per compute
+// stream) should together fill the resident warps of the state march exactly once -- 148 SMs x 12 warps at the 168-register
+// budget -- and not spill into a second, nearly empty wave. Measured on C2: 13 slabs of 10 tiles on 3
+// streams (3 x 10 x 58 lines = 1740 of 1776 slots).
+static int host_slab_count(const awfl_handle *h) {
+  const Geom &g = h->g;
+  const int tiles = (g.nens + 31) / 32;
+  if (h->host_slabs > 0) return h->host_slabs < tiles ? h->host_slabs : tiles;
+  const int nc = h->host_cstreams > 4 ? 4 : (h->host_cstreams < 1 ? 1 : h->host_cstreams);
+  const long lines = (long)g.nz * g.ny;                 // x-march blocks per member tile
+  long per_slab = (148L * 12) / (nc * lines);
+  if (per_slab < 1) per_slab = 1;
+  long P = (tiles + per_slab - 1) / per_slab;
+  if (P > 16) P = 16;
+  return (int)P;
+}
+int awfl_host_slabs(const awfl_handle *h) { return host_slab_count(h); }
 
 // Dycore::timeStep on HOST fields, pipelined over member slabs (multiples of 32 members; a slab is a strided column
 // block of every (cells, nens) field: cudaMemcpy2DAsync, row = the slab's members of one cell).
 //   copy-in stream : H2D of slab s, then its conversion kernel (+ CFL minimum)        s = 0..P-1, then the dt read-back
 //   compute stream : the SSPRK3 sub-cycles of slab s as soon as its conversion is done
-//   copy-out stream: dycore -> coupler conversion of slab s, then its D2H
+//   copy-out stream: dycore -> coupler conversion of slab s into the RESULT staging, then its D2H
 // The reference takes dt from the whole coupler (Dycore.h:141-145), so the sub-cycle count is only known when the LAST
-// slab has arrived. To overlap the copies with the kernels anyway the slabs start with a PREDICTED count -- the caller's
-// ncycles_override, else the count the previous call derived -- and nothing irreversible happens until the prediction is
-// checked against the CFL minimum over all members: the staged inputs stay untouched on the device (the out-conversion and
-// the D2H of every slab are only enqueued after the check), so a wrong prediction costs one plain, un-overlapped step
-// from those inputs and never changes a result. Without a prediction (first call) the slabs wait for the dt.
+// slab has arrived. To overlap the copies with the kernels anyway the slabs run with a PREDICTED count -- the caller's
+// ncycles_override, else the count the previous call derived -- all the way to the host buffers, and the prediction is
+// checked against the CFL minimum over all members afterwards. The staged inputs stay untouched on the device (results
+// go to a second staging buffer), so a wrong prediction costs one plain, un-overlapped step from those inputs, whose
+// results then overwrite what the speculative pass wrote to the host buffers; it never changes a result. Without a
+// prediction (first call) the slabs wait for the dt.
 // Results are identical to awfl_time_step on the same fields for any slab count (members never interact).
 int awfl_time_step_host(awfl_handle *h, double *const *host_fields, double crm_dt, int ncycles_override, int *ncycles_out) {
   if (!(crm_dt > 0.0)) return fail(h, "awfl_time_step_host: crm_dt must be positive");
+  // AWFL_HOST_TRACE=1: device timeline of this call on stderr (timing events on the three streams; diagnostic only)
+  static const bool trace = getenv("AWFL_HOST_TRACE") && atoi(getenv("AWFL_HOST_TRACE")) > 0;
+  std::vector<std::pair<std::string, cudaEvent_t>> marks;
+  auto mark = [&](const char *what, int s, cudaStream_t st) {
+    if (!trace) return;
+    cudaEvent_t e;
+    cudaEventCreate(&e);
+    cudaEventRecord(e, st);
+    marks.push_back({std::string(what) + "[" + std::to_string(s) + "]", e});
+  };
   const Geom &g = h->g;
   const int N = NS + g.nt;
   const size_t fb = sizeof(double) * (size_t)g.ncell;
   if (!h->stage_fields) CK(cudaMalloc((void **)&h->stage_fields, fb * N));
+  if (!h->stage_out) CK(cudaMalloc((void **)&h->stage_out, fb * N));
   const int tiles = (g.nens + 31) / 32;
-  const int P = h->host_slabs < tiles ? h->host_slabs : tiles;
+  const int P = host_slab_count(h);
   if (!h->s_in) {
     CK(cudaStreamCreateWithFlags(&h->s_in, cudaStreamNonBlocking));
     CK(cudaStreamCreateWithFlags(&h->s_out, cudaStreamNonBlocking));
+    for (int c = 0; c < 4; c++) CK(cudaStreamCreateWithFlags(&h->s_cmp[c], cudaStreamNonBlocking));
   }
-  while ((int)h->slab_ev.size() < 2 * P + 1) {
+  while ((int)h->slab_ev.size() < 2 * P + 3) {
     cudaEvent_t e;
     CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     h->slab_ev.push_back(e);
   }
-  std::vector<double *> trp(g.nt);
+  std::vector<double *> trp(g.nt), trpo(g.nt);
   awfl_fields f;
   f.density_dry = h->stage_fields; f.uvel = h->stage_fields + g.ncell; f.vvel = h->stage_fields + 2 * g.ncell;
   f.wvel = h->stage_fields + 3 * g.ncell; f.temp = h->stage_fields + 4 * g.ncell;
   for (int t = 0; t < g.nt; t++) trp[t] = h->stage_fields + (size_t)(NS + t) * g.ncell;
   f.tracers = trp.data();
-  FieldPtrs fp;
+  FieldPtrs fp, fpo;
   if (make_field_ptrs(h, &f, fp)) return 1;
+  for (int v = 0; v < NS; v++) fpo.f[v] = h->stage_out + (size_t)v * g.ncell;
+  for (int t = 0; t < g.nt; t++) trpo[t] = h->stage_out + (size_t)(NS + t) * g.ncell;
+  fpo.tr = h->trptr_out_d;
+  if (g.nt > 0) CK(cudaMemcpyAsync(h->trptr_out_d, trpo.data(), sizeof(double *) * g.nt, cudaMemcpyHostToDevice, h->stream));
   const bool need_dt = ncycles_override <= 0;
   if (need_dt) {
     const double inf = INFINITY;
     CK(cudaMemcpyAsync(h->dt_min_d, &inf, sizeof(double), cudaMemcpyHostToDevice, h->stream));
   }
   if (ensure_cvtab(h)) return 1;
-  // the copy-in stream must not run ahead of earlier work on the compute stream (staging buffer, tracer pointer table,
+  // the copy streams must not run ahead of earlier work on the compute stream (staging buffers, tracer pointer tables,
   // dt reset)
   CK(cudaEventRecord(h->slab_ev[2 * P], h->stream));
   CK(cudaStreamWaitEvent(h->s_in, h->slab_ev[2 * P], 0));
+  CK(cudaStreamWaitEvent(h->s_out, h->slab_ev[2 * P], 0));
+  const bool alt = h->host_cstreams > 1 && P > 1;
+  const int nc = h->host_cstreams > 4 ? 4 : h->host_cstreams;
+  if (alt) for (int c = 0; c < nc; c++) CK(cudaStreamWaitEvent(h->s_cmp[c], h->slab_ev[2 * P], 0));
+  cudaStream_t const user_stream = h->stream;
+  mark("start", 0, h->s_in);
   const int predicted = need_dt ? h->host_last_ncycles : ncycles_override;
   int qi = 0;   // buffer that holds the advanced state (the same for every slab: it depends on the sub-cycle count only)
   std::vector<Geom> slab(P, g);
   const size_t rows = (size_t)g.nz * g.ny * g.nx, pitch = sizeof(double) * (size_t)g.nens;
+  // the sub-cycles of slab s on its compute stream, after event `after` (the launch helpers enqueue on h->stream)
+  auto advance_slab = [&](int s, int n, double dts, int after) -> int {
+    h->stream = alt ? h->s_cmp[s % nc] : user_stream;
+    cudaError_t e = cudaStreamWaitEvent(h->stream, h->slab_ev[after], 0);
+    mark("advance_start", s, h->stream);
+    if (e == cudaSuccess) {
+      qi = step_advance(h, slab[s], n, dts);
+      mark("advanced", s, h->stream);
+      e = cudaEventRecord(h->slab_ev[2 * s + 1], h->stream);
+    }
+    h->stream = user_stream;
+    if (e != cudaSuccess) return fail(h, std::string("awfl_time_step_host: ") + cudaGetErrorString(e));
+    return 0;
+  };
+  // results of slab s: conversion into the result staging + D2H, on the copy-out stream, after event 2s+1
+  auto results_out = [&](int s) -> int {
+    CK(cudaStreamWaitEvent(h->s_out, h->slab_ev[2 * s + 1], 0));
+    step_convert_out(h, slab[s], fpo, qi, h->s_out);
+    mark("converted_out", s, h->s_out);
+    for (int v = 0; v < N; v++) {
+      if (P == 1) CK(cudaMemcpyAsync(host_fields[v], h->stage_out + (size_t)v * g.ncell, fb, cudaMemcpyDeviceToHost, h->s_out));
+      else CK(cudaMemcpy2DAsync(host_fields[v] + slab[s].e0, pitch, h->stage_out + (size_t)v * g.ncell + slab[s].e0, pitch,
+                                sizeof(double) * (size_t)slab[s].ne, rows, cudaMemcpyDeviceToHost, h->s_out));
+    }
+    mark("d2h_done", s, h->s_out);
+    return 0;
+  };
   for (int s = 0; s < P; s++) {
     const int t0 = (int)((long)tiles * s / P), t1 = (int)((long)tiles * (s + 1) / P);
     slab[s].e0 = 32 * t0;
@@ -1214,12 +1291,12 @@ int awfl_time_step_host(awfl_handle *h, double *const *host_fields, double crm_d
       else CK(cudaMemcpy2DAsync(h->stage_fields + (size_t)v * g.ncell + slab[s].e0, pitch, host_fields[v] + slab[s].e0, pitch,
                                 sizeof(double) * (size_t)slab[s].ne, rows, cudaMemcpyHostToDevice, h->s_in));
     }
+    mark("h2d_done", s, h->s_in);
     step_convert_in(h, slab[s], fp, need_dt, h->s_in);
     CK(cudaEventRecord(h->slab_ev[2 * s], h->s_in));
     if (predicted > 0) {
-      CK(cudaStreamWaitEvent(h->stream, h->slab_ev[2 * s], 0));
-      qi = step_advance(h, slab[s], predicted, crm_dt / predicted);
-      CK(cudaEventRecord(h->slab_ev[2 * s + 1], h->stream));
+      if (advance_slab(s, predicted, crm_dt / predicted, 2 * s)) return 1;
+      if (results_out(s)) return 1;
     }
   }
   int ncycles = ncycles_override;
@@ -1227,33 +1304,34 @@ int awfl_time_step_host(awfl_handle *h, double *const *host_fields, double crm_d
   h->host_last_ncycles = ncycles;
   const double dt = crm_dt / ncycles;       // Dycore.h:145
   if (predicted > 0 && predicted != ncycles) {
-    // misprediction: redo the whole step from the staged inputs (still intact), un-overlapped
+    // misprediction: let the speculative pass drain, then redo the whole step from the staged inputs (still intact),
+    // un-overlapped; its results overwrite the speculative ones in the host buffers
     h->host_mispredictions++;
+    CK(cudaStreamSynchronize(h->s_out));
     step_convert_in(h, g, fp, false);
     qi = step_advance(h, g, ncycles, dt);
-    step_convert_out(h, g, fp, qi);
+    step_convert_out(h, g, fpo, qi);
     CK(cudaEventRecord(h->slab_ev[1], h->stream));
     CK(cudaStreamWaitEvent(h->s_out, h->slab_ev[1], 0));
-    for (int v = 0; v < N; v++) CK(cudaMemcpyAsync(host_fields[v], h->stage_fields + (size_t)v * g.ncell, fb, cudaMemcpyDeviceToHost, h->s_out));
-  } else {
+    for (int v = 0; v < N; v++) CK(cudaMemcpyAsync(host_fields[v], h->stage_out + (size_t)v * g.ncell, fb, cudaMemcpyDeviceToHost, h->s_out));
+  } else if (predicted <= 0) {
     for (int s = 0; s < P; s++) {
-      if (predicted <= 0) {
-        if (s == 0) CK(cudaStreamWaitEvent(h->stream, h->slab_ev[2 * (P - 1)], 0));
-        qi = step_advance(h, slab[s], ncycles, dt);
-        CK(cudaEventRecord(h->slab_ev[2 * s + 1], h->stream));
-      }
-      CK(cudaStreamWaitEvent(h->s_out, h->slab_ev[2 * s + 1], 0));
-      step_convert_out(h, slab[s], fp, qi, h->s_out);
-      for (int v = 0; v < N; v++) {
-        if (P == 1) CK(cudaMemcpyAsync(host_fields[v], h->stage_fields + (size_t)v * g.ncell, fb, cudaMemcpyDeviceToHost, h->s_out));
-        else CK(cudaMemcpy2DAsync(host_fields[v] + slab[s].e0, pitch, h->stage_fields + (size_t)v * g.ncell + slab[s].e0, pitch,
-                                  sizeof(double) * (size_t)slab[s].ne, rows, cudaMemcpyDeviceToHost, h->s_out));
-      }
+      if (advance_slab(s, ncycles, dt, 2 * (P - 1))) return 1;      // the dt needed every slab's conversion
+      if (results_out(s)) return 1;
     }
   }
   CK(cudaGetLastError());
   CK(cudaStreamSynchronize(h->s_out));
+  if (alt) for (int c = 0; c < nc; c++) CK(cudaStreamSynchronize(h->s_cmp[c]));
   CK(cudaStreamSynchronize(h->stream));
+  if (trace) {
+    for (size_t m = 1; m < marks.size(); m++) {
+      float ms = 0.f;
+      cudaEventElapsedTime(&ms, marks[0].second, marks[m].second);
+      fprintf(stderr, "awfl_time_step_host %-18s %8.3f ms\n", marks[m].first.c_str(), ms);
+    }
+    for (auto &m : marks) cudaEventDestroy(m.second);
+  }
   if (ncycles_out) *ncycles_out = ncycles;
   return 0;
 }

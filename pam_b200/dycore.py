@@ -233,6 +233,11 @@ class Dycore:
         """Member slabs pipelined by time_step_host (copies of one slab overlap the kernels of another)."""
         self._rc(self.lib.awfl_set_host_slabs(self.h, int(nslabs)), "awfl_set_host_slabs")
 
+
+    def host_slabs(self):
+        """Slab count the next time_step_host will use (0 passed to set_host_slabs = chosen from the grid)."""
+        return int(self.lib.awfl_host_slabs(self.h))
+
     def host_mispredictions(self):
         """Calls of time_step_host whose predicted sub-cycle count was wrong (redone un-overlapped)."""
         return self.lib.awfl_host_mispredictions(self.h)

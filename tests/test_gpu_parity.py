@@ -191,11 +191,12 @@ def test_fixed_ncycles_and_host_buffer_entry_point_agree():
         assert np.array_equal(a, got[n]), n      # same kernels, same inputs: bit-identical
 
 
-@pytest.mark.parametrize("nens,slabs,ny", [(100, 1, 1), (100, 3, 1), (100, 4, 1), (40, 8, 1), (70, 2, 3)])
+@pytest.mark.parametrize("nens,slabs,ny", [(100, 1, 1), (100, 3, 1), (100, 4, 1), (40, 8, 1), (70, 2, 3), (200, 7, 1), (100, 0, 1)])
 def test_host_buffer_member_slabs_are_bit_identical(nens, slabs, ny):
-    """awfl_time_step_host pipelines member slabs (copy/compute overlap); CRMs are independent and the CFL dt is taken
-    over all members before any slab advances, so every slab count must give the bits of the device-resident step --
-    including a ragged last slab (nens not a multiple of 32) and more slabs than 32-member tiles."""
+    """awfl_time_step_host pipelines member slabs (copy/compute overlap, consecutive slabs on alternating compute
+    streams); CRMs are independent and the sub-cycle count is that of the CFL dt over all members, so every slab count
+    (0 = chosen from the grid) must give the bits of the device-resident step -- including a ragged last slab (nens not
+    a multiple of 32) and more slabs than 32-member tiles."""
     case = syn.make_case(12, ny, 10 if ny == 1 else 6, nens, tracers=syn.TRACERS_NT1, grid="tanh")
     c, d = H.make_gpu(case, 5, crm_dt=2.0)
     d.declare_current_profile_as_hydrostatic(c)

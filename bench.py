@@ -160,8 +160,12 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--host-slabs", type=int, default=0, help="member slabs pipelined by the host-buffer entry point (0 = library default)")
+    ap.add_argument("--nens", type=int, default=0, help="experiments: override the members per GPU of the workload")
     args = ap.parse_args()
     w = dict(WORKLOADS[args.workload])
+    if args.nens > 0:
+        w["desc"] = w["desc"].replace("nens=%d" % w["nens"], "nens=%d" % args.nens)
+        w["nens"] = args.nens
     if args.ord:
         w["ord"] = args.ord
         w["desc"] = w["desc"].replace("ord=5", "ord=%d" % args.ord)
@@ -182,6 +186,8 @@ def main():
         raise RuntimeError("bench.py needs a CUDA device: the AWFL path has no CPU fallback")
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    from pam_b200.parallel import bind_to_gpu_numa_node
+    numa = bind_to_gpu_numa_node(local_rank) if world > 1 and not os.environ.get("AWFL_NO_NUMA_BIND") else None
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
 
@@ -276,7 +282,7 @@ def main():
         fb = 8 * ncell * len(names)
         e2e = {"value": float(eu.item()) / float(te.item()), "unit": "cell-updates/s", "h2d_bytes_per_step": fb * world,
                "d2h_bytes_per_step": fb * world, "steps": nst,
-               "host_slabs": d.host_slabs(),
+               "host_slabs": d.host_slabs(), "numa": numa,
                "note": "awfl_time_step_host: pinned host fields -> device, Dycore::timeStep, device -> host, every step; the ensemble "
                        "is pipelined in member slabs so that copies of one slab overlap the kernels of another"}
 

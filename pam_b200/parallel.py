@@ -41,3 +41,38 @@ def global_min_dt(local_dt, group=None, device=None):
             t = t.to(device if device is not None else torch.device("cuda", torch.cuda.current_device()))
         dist.all_reduce(t, op=dist.ReduceOp.MIN, group=group)
     return float(t.item())
+
+
+def _parse_cpulist(text):
+    cpus = set()
+    for part in text.strip().split(","):
+        if not part:
+            continue
+        a, _, b = part.partition("-")
+        cpus.update(range(int(a), int(b or a) + 1))
+    return cpus
+
+
+def bind_to_gpu_numa_node(device_index, sysfs="/sys"):
+    """Pin the calling process to the CPUs of the NUMA node its GPU hangs off, BEFORE it allocates host buffers: the
+    first touch then places the (pinned) coupler fields in that node's memory, so the H2D/D2H streams of the host-buffer
+    entry point do not cross the socket interconnect -- with 8 ranks x 2 x 55 GB/s that is what decides the e2e rate.
+    Returns {"node": n, "cpus": count} or None when the topology is not visible (no sysfs entry, single node, or the
+    node's CPUs are outside this process's affinity mask). E3SM places MPI ranks the same way through its launcher."""
+    import os
+    try:
+        p = torch.cuda.get_device_properties(device_index)
+        bdf = "%04x:%02x:%02x.0" % (p.pci_domain_id, p.pci_bus_id, p.pci_device_id)
+        with open(os.path.join(sysfs, "bus/pci/devices", bdf, "numa_node")) as fh:
+            node = int(fh.read().strip())
+        if node < 0:
+            return None
+        with open(os.path.join(sysfs, "devices/system/node/node%d/cpulist" % node)) as fh:
+            cpus = _parse_cpulist(fh.read())
+        cpus &= os.sched_getaffinity(0)
+        if not cpus:
+            return None
+        os.sched_setaffinity(0, cpus)
+        return {"node": node, "cpus": len(cpus)}
+    except (OSError, ValueError, AttributeError):
+        return None

@@ -64,3 +64,33 @@ def test_two_rank_ensemble_sharding_matches_single_process(tmp_path):
         assert np.allclose(r["gm"], mass.mean(axis=1), rtol=1e-14, atol=0)
         assert float(r["dt_glob"]) == min(float(x["dt_local"]) for x in ranks)
     assert abs(min(float(x["dt_local"]) for x in ranks) - dt_all) <= 1e-15 * dt_all
+
+
+def test_bind_to_gpu_numa_node_on_a_fake_topology(tmp_path, monkeypatch):
+    """Rank placement for the host-buffer path: the process is pinned to the CPUs of its GPU's NUMA node (sysfs walk),
+    and left alone when the topology is not visible."""
+    import types
+    import torch
+    from pam_b200 import parallel as P
+    props = types.SimpleNamespace(pci_domain_id=0, pci_bus_id=0x1b, pci_device_id=0)
+    monkeypatch.setattr(torch.cuda, "get_device_properties", lambda i: props)
+    allowed = sorted(os.sched_getaffinity(0))
+    dev = tmp_path / "bus/pci/devices/0000:1b:00.0"
+    dev.mkdir(parents=True)
+    (dev / "numa_node").write_text("1\n")
+    node = tmp_path / "devices/system/node/node1"
+    node.mkdir(parents=True)
+    (node / "cpulist").write_text("%d\n" % allowed[0])
+    try:
+        assert P.bind_to_gpu_numa_node(0, sysfs=str(tmp_path)) == {"node": 1, "cpus": 1}
+        assert os.sched_getaffinity(0) == {allowed[0]}
+    finally:
+        os.sched_setaffinity(0, allowed)
+    (dev / "numa_node").write_text("-1\n")
+    assert P.bind_to_gpu_numa_node(0, sysfs=str(tmp_path)) is None
+    (dev / "numa_node").write_text("1\n")
+    (node / "cpulist").write_text("100000-100003\n")                     # CPUs outside this process's mask
+    assert P.bind_to_gpu_numa_node(0, sysfs=str(tmp_path)) is None
+    assert P.bind_to_gpu_numa_node(0, sysfs=str(tmp_path / "nowhere")) is None
+    assert os.sched_getaffinity(0) == set(allowed)
+    assert P._parse_cpulist("0-3,8,10-11\n") == {0, 1, 2, 3, 8, 10, 11}

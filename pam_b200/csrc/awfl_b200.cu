@@ -834,13 +834,13 @@ static int ensure_cvtab(awfl_handle *h) {
 
 static void launch_state_sweep(awfl_handle *h, const Geom &g, int dir, int mode, const SweepArgs &a) {
   ProfScope ps(h, KC_STATE_X + dir);
-  AWFL_ORD_DISPATCH(march_state(h->stream, g, h->ph, a, dir, mode, dir == 2 ? (h->use_cvtab ? 1 : 2) : 0));
+  AWFL_ORD_DISPATCH(march_state(h->stream, g, h->ph, a, dir, mode, dir == 2 ? (h->use_cvtab ? 1 : (h->shared_grid && mode == 1 ? 3 : 2)) : 0));
 }
 
 static void launch_tracer_sweep(awfl_handle *h, const Geom &g, int dir, TracerSweepArgs a) {
   if (g.nt == 0) return;
   ProfScope ps(h, KC_TRACER_X + dir);
-  AWFL_ORD_DISPATCH(march_tracer(h->stream, g, a, dir, dir == 2 ? (h->use_cvtab ? 1 : 2) : 0));
+  AWFL_ORD_DISPATCH(march_tracer(h->stream, g, a, dir, dir == 2 ? (h->use_cvtab ? 1 : (h->shared_grid ? 3 : 2)) : 0));
 }
 
 // One semi-discrete right-hand side + stage combination.

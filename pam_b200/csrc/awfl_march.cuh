@@ -100,7 +100,8 @@ __device__ __forceinline__ EOn<NV> weno_ring_inl(const double *fb, int head, M m
 }
 
 // Matrix provider of a step: VT 0 = constant horizontal tables, 1 = vertical tables in the constant bank (all members
-// share one vertical grid), 2 = vertical tables in global memory (member-dependent grid, or table too large).
+// share one vertical grid), 2 = vertical tables in global memory with a run-time element stride (member-dependent grid),
+// 3 = in global memory with unit stride (shared grid whose table is too large for the constant bank).
 template <int ORD, int VT> struct MatSel;
 template <int ORD> struct MatSel<ORD, 0> {
   using type = HMat<ORD>;
@@ -114,6 +115,13 @@ template <int ORD> struct MatSel<ORD, 2> {
   using type = VMat<ORD>;
   static __device__ __forceinline__ type get(const double *vtab, long vst, long voff, int level) {
     type m; m.p = vtab + (long)level * VMat<ORD>::NEL * vst + voff; m.st = vst; return m;
+  }
+};
+
+template <int ORD> struct MatSel<ORD, 3> {
+  using type = UMat<ORD>;
+  static __device__ __forceinline__ type get(const double *vtab, long, long, int level) {
+    type m; m.p = vtab + (long)level * UMat<ORD>::NEL; return m;
   }
 };
 

@@ -42,6 +42,7 @@ void OrdLaunch<ORD>::march_state(cudaStream_t s, const Geom &g, const Phys &ph, 
   else if (dir == 1) AWFL_LAUNCH_MARCH((k_march_state<ORD, 1, 0, 0>), B, g, ph, a);
   else if (mode == 1) {
     if (vt == 1) AWFL_LAUNCH_MARCH((k_march_state<ORD, 2, 1, 1>), B, g, ph, a);
+    else if (vt == 3) AWFL_LAUNCH_MARCH((k_march_state<ORD, 2, 1, 3>), B, g, ph, a);
     else AWFL_LAUNCH_MARCH((k_march_state<ORD, 2, 1, 2>), B, g, ph, a);
   } else {
     if (vt == 1) AWFL_LAUNCH_MARCH((k_march_state<ORD, 2, 2, 1>), B, g, ph, a);
@@ -56,6 +57,7 @@ void OrdLaunch<ORD>::march_tracer(cudaStream_t s, const Geom &g, const TracerSwe
   if (dir == 0) AWFL_LAUNCH_MARCH((k_march_tracer<ORD, 0, 0>), B, g, a);
   else if (dir == 1) AWFL_LAUNCH_MARCH((k_march_tracer<ORD, 1, 0>), B, g, a);
   else if (vt == 1) AWFL_LAUNCH_MARCH((k_march_tracer<ORD, 2, 1>), B, g, a);
+  else if (vt == 3) AWFL_LAUNCH_MARCH((k_march_tracer<ORD, 2, 3>), B, g, a);
   else AWFL_LAUNCH_MARCH((k_march_tracer<ORD, 2, 2>), B, g, a);
 }
 

@@ -125,6 +125,18 @@ template <int ORD> struct VMat {
   __device__ __forceinline__ double hi(int r, int s) const { return __ldg(p + (HS * HS * HS + r * ORD + s) * st); }
 };
 
+// The same table for a grid shared by all ensemble members when it does not fit the constant bank (ord 9 at 58 levels):
+// unit element stride known at compile time, so every element is a load at an immediate offset from the level's base --
+// no 64-bit address arithmetic per element (with a run-time stride the ord-9 z march executed more IMAD than DFMA).
+template <int ORD> struct UMat {
+  static constexpr bool is_const = false;
+  static constexpr int HS = (ORD + 1) / 2;
+  static constexpr int NEL = HS * HS * HS + ORD * ORD;
+  const double *p;
+  __device__ __forceinline__ double lo(int i, int r, int s) const { return __ldg(p + ((i * HS + r) * HS + s)); }
+  __device__ __forceinline__ double hi(int r, int s) const { return __ldg(p + (HS * HS * HS + r * ORD + s)); }
+};
+
 // Vertical matrices of a grid shared by all ensemble members, held in the constant bank: the level index is uniform
 // across a warp of the marching kernels, so every element is one constant-cache load (no vector-memory traffic).
 // Same per-level layout as VMat. Uploaded by OrdLaunch<ORD>::upload_cvtab.

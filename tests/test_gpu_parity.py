@@ -109,6 +109,7 @@ def test_tendencies_match_oracle(cfg):
     dict(ord=5, ny=6, nx=8, nz=10, nens=33),
     dict(ord=5, nt=10, nens=32),
     dict(ord=3), dict(ord=7), dict(ord=9, nz=12),
+    dict(ord=9, nz=40, nx=10, nens=33),      # vertical table too large for the constant bank: unit-stride global table
 ])
 def test_one_step_matches_oracle(cfg):
     cfg = dict(cfg)
@@ -254,6 +255,23 @@ def test_fused_fct_update_matches_two_kernel_path(nx, nz, nens, monkeypatch):
         assert np.linalg.norm(a - b) <= 1e-13 * max(np.linalg.norm(b), floor), k
         if k not in H.STATE_FIELDS:
             assert a.min() >= 0.0, k
+
+
+@pytest.mark.parametrize("ord", [5, 9])
+def test_vertical_table_homes_give_the_same_bits(ord, monkeypatch):
+    """The vertical matrices of a shared grid live in the constant bank when they fit, else in global memory (unit
+    stride); member-dependent grids use a strided global table. Same numbers, same arithmetic: identical bits."""
+    case = _case(nz=14, nx=10, nens=40)
+    out = {}
+    for no_c in ("0", "1"):
+        if no_c == "1":
+            monkeypatch.setenv("AWFL_NO_CVTAB", "1")
+        c, d = H.make_gpu(case, ord, crm_dt=2.0)
+        d.declare_current_profile_as_hydrostatic(c)
+        d.timeStep(c)
+        out[no_c] = H.gpu_fields(c)
+    for k in out["0"]:
+        assert np.array_equal(out["0"][k], out["1"][k]), k
 
 
 def test_errors_are_reported_not_swallowed():

@@ -3,6 +3,7 @@
 (cudaMemcpy2DAsync rows of 2/4/8/32 KB), one direction and both at once. Diagnostic for DESIGN.md 5 (e2e)."""
 import ctypes as C
 import json
+import sys
 import torch
 
 rt = C.CDLL("libcudart.so.12")
@@ -37,7 +38,7 @@ def timed(fn, reps=5):
 
 
 out = {}
-for ne in (4096, 1024, 512, 256):
+for ne in ((1024,) if '--quick' in sys.argv else (4096, 1024, 512, 256)):   # --quick: 8 KB rows only (run one per GPU at once)
     out["h2d_row%dB" % (8 * ne)] = nbytes / timed(lambda: copy2d(dev, host, H2D, ne, s1)) / 1e6
     out["d2h_row%dB" % (8 * ne)] = nbytes / timed(lambda: copy2d(host2, dev2, D2H, ne, s2)) / 1e6
     out["both_row%dB_each" % (8 * ne)] = nbytes / timed(lambda: (copy2d(dev, host, H2D, ne, s1), copy2d(host2, dev2, D2H, ne, s2))) / 1e6

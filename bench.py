@@ -110,7 +110,7 @@ def cpu_reference_rate(w, seconds_target=12.0, warm=1, steps=None, nens=None):
     if not reflib.available(w["ord"], omp=True):
         raise RuntimeError("oracle/_ref/libpam_ref_ord%d_omp.so is missing (build it with __graft_entry__.build() where "
                            "/root/reference exists)" % w["ord"])
-    nens = nens or max(8, min(w["nens"], 2 * cores))
+    nens = nens or max(8, min(w["nens"], 8 * cores))    # bounded sample: 8 members per host thread
     case = build_case(w, nens=nens)
     r = reflib.RefDycore(w["nz"], w["ny"], w["nx"], nens, case["xlen"], case["ylen"], case["zint"], tracers=case["tracers"],
                          consts=case["consts"], crm_dt=CRM_DT, ord=w["ord"], omp=True)

@@ -633,6 +633,7 @@ struct awfl_handle {
   int host_cstreams;                     // 1 = all slabs on the handle's stream, 2..4 = round robin over s_cmp
   std::vector<cudaEvent_t> slab_ev;      // 2 events per slab: inputs on the device / results ready on the device
   double *tmp_state;     // scratch for awfl_compute_tendencies
+  double *pcache;        // pressure of the current stage input (SweepArgs::pcache)
 };
 
 static std::string g_create_err;
@@ -856,7 +857,7 @@ static void run_stage(awfl_handle *h, const Geom &g, const double *qin, const do
     const bool last = d == ndir - 1;
     SweepArgs s;
     s.qin = qin; s.qbase = q0; s.qout = mode == 2 ? st_out : qout; s.tend = h->tend; s.mflux = h->mflux[dir];
-    s.dz = h->dz; s.grav_var = h->grav_var; s.vtab = h->vtab; s.rdz = h->rdz; s.vst = h->shared_grid ? 1 : g.nens;
+    s.dz = h->dz; s.grav_var = h->grav_var; s.vtab = h->vtab; s.rdz = h->rdz; s.pcache = h->pcache; s.vst = h->shared_grid ? 1 : g.nens;
     s.a = a; s.b = b; s.c = b * dt_full; s.first = d == 0; s.sbits = sbits_for(h, nn[dir]); s.labits = labits_for(h, dir);
     launch_state_sweep(h, g, dir, last ? mode : 0, s);
     TracerSweepArgs t;
@@ -966,6 +967,7 @@ int awfl_create(const awfl_config *cfg, awfl_handle **out) {
 #define ALLOC(ptr, bytes) do { if (cudaMalloc((void **)&(ptr), (bytes)) != cudaSuccess) return bail(std::string("cudaMalloc failed for ") + #ptr); } while (0)
   for (int b = 0; b < 3; b++) ALLOC(h->Q[b], fb * N);
   ALLOC(h->tend, fb * NS);
+  ALLOC(h->pcache, fb);
   ALLOC(h->mflux[0], fb); ALLOC(h->mflux[1], fb); ALLOC(h->mflux[2], fb + lvl);
   ALLOC(h->tflux[0], fb * nt); ALLOC(h->tflux[1], fb * nt); ALLOC(h->tflux[2], (fb + lvl) * nt);
   ALLOC(h->mult, fb * nt);
@@ -1017,7 +1019,7 @@ void awfl_destroy(awfl_handle *h) {
   for (int o = 0; o < 4; o++) if (g_cvtab_owner[o] == h) g_cvtab_owner[o] = nullptr;
   cudaFree(h->mult); cudaFree(h->dz); cudaFree(h->rdz); cudaFree(h->grav_var); cudaFree(h->vtab); cudaFree(h->vs2c); cudaFree(h->vwrl);
   cudaFree(h->pint); cudaFree(h->dt_min_d); cudaFree(h->mass_d); cudaFree(h->positive_d); cudaFree(h->adds_mass_d);
-  cudaFree(h->trptr_d); cudaFree(h->trptr_out_d); cudaFree(h->stage_fields); cudaFree(h->stage_out); cudaFree(h->tmp_state);
+  cudaFree(h->pcache); cudaFree(h->trptr_d); cudaFree(h->trptr_out_d); cudaFree(h->stage_fields); cudaFree(h->stage_out); cudaFree(h->tmp_state);
   if (h->s_in) { cudaStreamDestroy(h->s_in); cudaStreamDestroy(h->s_out); for (int c = 0; c < 4; c++) cudaStreamDestroy(h->s_cmp[c]); }
   for (cudaEvent_t e : h->slab_ev) cudaEventDestroy(e);
   if (h->dt_min_h) cudaFreeHost(h->dt_min_h);

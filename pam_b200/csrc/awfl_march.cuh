@@ -50,7 +50,7 @@ template <int ORD> struct MarchCfg {
 // against 94 FP64-pipe instructions for the correctly rounded pow(): 49. Stated in DESIGN.md (tolerance budget).
 __device__ __forceinline__ double pow_pos(double x, double g) { return exp(g * log(x)); }
 
-struct Raw { double r, ru, rv, rw, rt; };
+struct Raw { double r, ru, rv, rw, rt, p; };
 
 // 8-byte asynchronous global -> shared copy (LDGSTS). Unlike a load into a register it is not tracked by the register
 // scoreboard, so it stays in flight across the call to weno_ring (a CALL waits for every pending register load:
@@ -172,6 +172,10 @@ k_march_state(const Geom g, const Phys ph, const SweepArgs a) {
     Raw x;
     x.r = __ldg(q + idx); x.ru = __ldg(q + nc + idx); x.rv = __ldg(q + 2 * nc + idx); x.rw = __ldg(q + 3 * nc + idx);
     x.rt = __ldg(q + 4 * nc + idx);
+    // the pressure C0 (rho theta)^gamma of a cell is the same in every direction of a stage: the x march (always the
+    // first sweep) computes it, the other marches read it back -- one x^gamma (~160 instructions) per cell and stage
+    // instead of one per direction
+    x.p = DIR == 0 ? 0.0 : __ldg(a.pcache + idx);
     return x;
   };
   // conserved -> primitives + pressure (Dycore.h:310-321); wall ghosts per Dycore.h:662-710 with the intended
@@ -180,7 +184,13 @@ k_march_state(const Geom g, const Phys ph, const SweepArgs a) {
     const double rinv = rcp_pos(x.r);
     double r = x.r, w = x.rw * rinv;
     double m = DIR == 0 ? x.ru : (DIR == 1 ? x.rv : x.rw);
-    double p = ph.C0 * pow_pos(x.rt, ph.gamma);
+    double p;
+    if (DIR == 0) {
+      p = ph.C0 * pow_pos(x.rt, ph.gamma);
+      if (c >= 0 && c < n) a.pcache[it.base + (long)c * sd] = p;
+    } else {
+      p = x.p;
+    }
     if (DIR == 2 && (c < 0 || c >= n)) {
       // hydrostatic constant-theta extrapolation: rho_g^(gamma-1) = rho0^(gamma-1) +- grav (gamma-1) dz0 dist / (gamma C0 theta0^gamma)
       // (Dycore.h:683-690, :697-704), with C0 theta0^gamma = p0 / rho0^gamma
@@ -360,7 +370,7 @@ k_march_tracer(const Geom g, const TracerSweepArgs a) {
     }
     const typename MatSel<ORD, VT>::type mat = MatSel<ORD, VT>::get(a.vtab, a.vst, voff, c + 1);
     EOn<NL> eo;
-    if constexpr (VT != 2) eo = weno_ring<ORD, NL>(rb, head, mat); else eo = weno_ring_inl<ORD, NL>(rb, head, mat);
+    if constexpr (VT == 0) eo = weno_ring<ORD, NL>(rb, head, mat); else eo = weno_ring_inl<ORD, NL>(rb, head, mat);
 #pragma unroll
     for (int v = 0; v < NL; v++) {
       const double E = eo.E[v], O = eo.O[v];

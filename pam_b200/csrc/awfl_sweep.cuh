@@ -86,8 +86,10 @@ __device__ __forceinline__ bool decode_item(const Geom &g, int sbits, int labits
   it.tr = (int)(z >> (sbits + labits));
   it.lb = (int)blockIdx.y * LB_LINES;
   if (it.la >= la_count) return false;
+  // lanes past the last member of a ragged slab repeat that member (same values written twice) instead of leaving: with
+  // every lane alive the warp stays provably convergent and ptxas keeps loop control and table loads on the uniform path
   it.e = g.e0 + (int)blockIdx.x * 32 + (int)(threadIdx.x & 31);
-  if (it.e >= g.e0 + g.ne) return false;
+  if (it.e > g.e0 + g.ne - 1) it.e = g.e0 + g.ne - 1;
   it.c0 = (seg * n) >> sbits;
   it.c1 = ((seg + 1) * n) >> sbits;
   if (DIR == 0) it.base = (((long)it.la * g.ny + it.lb) * g.nx) * g.nens + it.e;          // (k,j)

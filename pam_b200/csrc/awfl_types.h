@@ -32,6 +32,7 @@ struct SweepArgs {
   const double *grav_var; // (nz,nens)
   const double *vtab;     // vertical matrices (global-memory copy)
   const double *rdz;      // 1/dz (nz,nens)
+  double *pcache;         // pressure of the stage input, one field: written by the x march, read by the y and z marches
   long vst;               // element stride of vtab: nens (member-dependent grid) or 1 (shared grid)
   double a, b, c;         // SSPRK3 stage coefficients (c = b*dt)
   int first;              // 1: this is the first sweep of the stage (tend is written, not accumulated)

@@ -258,7 +258,13 @@ k_march_state(const Geom g, const Phys ph, const SweepArgs a) {
           if (ld_q) cp_async8(stg + (2 * i + 1) * MT, a.qbase + lq * nc + idx);   // qout may alias qbase: read before the write below
         }
       }
-      const EOn<AWFL_NV> eo = weno_ring<ORD, AWFL_NV>(rb + (v0 * ORD) * MT, head, mat);
+      // vertical marches on a shared grid: inlined (uniform per-level table loads are not hoisted out of the cell loop, and
+      // without the call the ~100 argument / return moves per cell go away: z march 7.80 -> 7.33 ms). Horizontal marches
+      // and member-dependent grids keep the real call (see weno_ring; inlined they spill: measured 7.11 vs 6.78 ms in x,
+      // 0.5-2 KB of spills with the strided tables)
+      EOn<AWFL_NV> eo;
+      if constexpr (VT == 1 || VT == 3) eo = weno_ring_inl<ORD, AWFL_NV>(rb + (v0 * ORD) * MT, head, mat);
+      else eo = weno_ring<ORD, AWFL_NV>(rb + (v0 * ORD) * MT, head, mat);
       if (ld_t || ld_q) cp_async_wait();
 #pragma unroll
       for (int i = 0; i < AWFL_NV; i++) {

@@ -41,7 +41,11 @@ enum { RF_M = 0, RF_P, RF_U, RF_V, RF_W, RF_T, RF_R, RF_COUNT };
 #define AWFL_V0_UNROLL_Z 1
 #endif
 #ifndef AWFL_NV
-#define AWFL_NV 2      // reconstructions evaluated together in the state march (1 or 2)
+#define AWFL_NV 2      // reconstructions evaluated together in the vertical state march (and everywhere above ord 5)
+#endif
+#ifndef AWFL_NV_H
+#define AWFL_NV_H 3    // ... in the horizontal state marches up to ord 5 (two calls per cell instead of three: x 6.33 -> 6.20 ms;
+                       // three at a time spill in the vertical march: 9.55 vs 7.33 ms)
 #endif
 
 template <int ORD> struct MarchCfg {
@@ -51,7 +55,7 @@ template <int ORD> struct MarchCfg {
   static constexpr int MINB_TR = ORD == 3 ? 20 : (ORD == 5 ? AWFL_MINB5_TR : 8);
   // per thread: the window ring (RF_COUNT fields x ORD cells) + the previous interface's 5 fluxes + 4 right-edge values
   // + a staging area for the read-modify-write operands (partial tendency, base state) of the group being reconstructed
-  static constexpr int COLS_STATE = RF_COUNT * ORD + NS + 4 + 2 * AWFL_NV;
+  static constexpr int COLS_STATE = RF_COUNT * ORD + NS + 4 + 2 * (AWFL_NV > AWFL_NV_H ? AWFL_NV : AWFL_NV_H);
   static constexpr size_t SMEM_STATE = (size_t)COLS_STATE * MT * sizeof(double);
   static constexpr size_t SMEM_TRACER = (size_t)(2 * (ORD + 3)) * MT * sizeof(double);   // two lines per warp
 };
@@ -160,7 +164,8 @@ k_march_state(const Geom g, const Phys ph, const SweepArgs a) {
   constexpr double cs = 350.0;             // Dycore.h:335
   constexpr double rcs = 1.0 / 350.0;
   constexpr int NORMAL = DIR == 0 ? idU : (DIR == 1 ? idV : idW);
-  constexpr int V0_UNROLL = DIR == 2 ? AWFL_V0_UNROLL_Z : AWFL_V0_UNROLL_H;   // unrolling of the loop over variable pairs
+  constexpr int NV = (DIR != 2 && ORD <= 5) ? AWFL_NV_H : AWFL_NV;             // reconstructions per group
+  constexpr int V0_UNROLL = DIR == 2 ? AWFL_V0_UNROLL_Z : AWFL_V0_UNROLL_H;   // unrolling of the loop over variable groups
   extern __shared__ double ring_smem[];
   Item it;
   // one warp per block: the march position depends on blockIdx only, so the compiler keeps the loop control and the
@@ -255,14 +260,14 @@ k_march_state(const Geom g, const Phys ph, const SweepArgs a) {
     const double rho = (upd_on && MODE != 0) ? rb[(RF_R * ORD) * MT + so] : 0.0;
     double rn = 0.0, pp = 0.0;
     bool up = false;
-    // reconstructed quantities in ring order: rho*u_n, p (acoustic pair), then u, v, w, theta -- AWFL_NV at a time
+    // reconstructed quantities in ring order: rho*u_n, p (acoustic pair), then u, v, w, theta -- NV at a time
 #pragma unroll(V0_UNROLL)
-    for (int v0 = 0; v0 < 6; v0 += AWFL_NV) {
+    for (int v0 = 0; v0 < 6; v0 += NV) {
       // start the asynchronous copies of this group's read-modify-write operands; they land while the group is
       // reconstructed
       const bool ld_t = upd_on && !a.first, ld_q = upd_on && MODE == 1 && a.a != 0.0;
 #pragma unroll
-      for (int i = 0; i < AWFL_NV; i++) {
+      for (int i = 0; i < NV; i++) {
         const int v = v0 + i, lq = v == 0 ? 0 : v - 1;
         if (v > 0) {
           if (ld_t) cp_async8(stg + (2 * i) * MT, a.tend + lq * nc + idx);
@@ -273,12 +278,12 @@ k_march_state(const Geom g, const Phys ph, const SweepArgs a) {
       // without the call the ~100 argument / return moves per cell go away: z march 7.80 -> 7.33 ms). Horizontal marches
       // and member-dependent grids keep the real call (see weno_ring; inlined they spill: measured 7.11 vs 6.78 ms in x,
       // 0.5-2 KB of spills with the strided tables)
-      EOn<AWFL_NV> eo;
-      if constexpr (VT == 1 || VT == 3) eo = weno_ring_inl<ORD, AWFL_NV>(rb + (v0 * ORD) * MT, head, mat);
-      else eo = weno_ring<ORD, AWFL_NV>(rb + (v0 * ORD) * MT, head, mat);
+      EOn<NV> eo;
+      if constexpr (VT == 1 || VT == 3) eo = weno_ring_inl<ORD, NV>(rb + (v0 * ORD) * MT, head, mat);
+      else eo = weno_ring<ORD, NV>(rb + (v0 * ORD) * MT, head, mat);
       if (ld_t || ld_q) cp_async_wait();
 #pragma unroll
-      for (int i = 0; i < AWFL_NV; i++) {
+      for (int i = 0; i < NV; i++) {
         const int v = v0 + i;
         const double E = eo.E[i], O = eo.O[i];
         if (v == 0) { mRs = E - O; mLns = E + O; continue; }

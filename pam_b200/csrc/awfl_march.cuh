@@ -55,7 +55,7 @@ template <int ORD> struct MarchCfg {
   static constexpr int MINB_TR = ORD == 3 ? 20 : (ORD == 5 ? AWFL_MINB5_TR : 8);
   // per thread: the window ring (RF_COUNT fields x ORD cells) + the previous interface's 5 fluxes + 4 right-edge values
   // + a staging area for the read-modify-write operands (partial tendency, base state) of the group being reconstructed
-  static constexpr int COLS_STATE = RF_COUNT * ORD + NS + 4 + 2 * (AWFL_NV > AWFL_NV_H ? AWFL_NV : AWFL_NV_H);
+  static constexpr int COLS_STATE = RF_COUNT * ORD + NS + 4 + 2 * NS;   // staging: (tend, base) of the 5 state variables
   static constexpr size_t SMEM_STATE = (size_t)COLS_STATE * MT * sizeof(double);
   static constexpr size_t SMEM_TRACER = (size_t)(2 * (ORD + 3)) * MT * sizeof(double);   // two lines per warp
 };
@@ -74,6 +74,13 @@ __device__ __forceinline__ void cp_async8(double *smem_dst, const double *gsrc) 
   asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(sa), "l"(gsrc) : "memory");
 }
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+// wait until at most `left` of the most recently committed groups are still in flight (left <= 2)
+__device__ __forceinline__ void cp_async_wait_left(int left) {
+  if (left >= 2) asm volatile("cp.async.wait_group 2;" ::: "memory");
+  else if (left == 1) asm volatile("cp.async.wait_group 1;" ::: "memory");
+  else asm volatile("cp.async.wait_group 0;" ::: "memory");
+}
 
 // NV reconstructions on consecutive ring columns. A real function call on purpose: inlined into the march loops, ptxas
 // hoists the ~80 loop-invariant constant-bank loads of the WENO tables out of the loop, runs out of uniform registers and
@@ -260,20 +267,30 @@ k_march_state(const Geom g, const Phys ph, const SweepArgs a) {
     const double rho = (upd_on && MODE != 0) ? rb[(RF_R * ORD) * MT + so] : 0.0;
     double rn = 0.0, pp = 0.0;
     bool up = false;
+    // Read-modify-write operands of cell c-1 (partial tendency, step-start state) arrive by asynchronous copies. Where the
+    // loop over the variable groups is unrolled (horizontal marches) ALL of them are started here, one commit group per
+    // variable group, and land while the groups are reconstructed; the rolled vertical march starts each group's copies
+    // right before its reconstruction (started here as well it spills 0.8 KB)
+    constexpr bool PRE_ALL = V0_UNROLL > 1;
+    const bool ld_t = upd_on && !a.first, ld_q = upd_on && MODE == 1 && a.a != 0.0;
+    auto start_copies = [&](int g0) {
+#pragma unroll
+      for (int i = 0; i < NV; i++) {
+        const int v = g0 + i;
+        if (v > 0) {
+          if (ld_t) cp_async8(stg + (2 * (v - 1)) * MT, a.tend + (v - 1) * nc + idx);
+          if (ld_q) cp_async8(stg + (2 * (v - 1) + 1) * MT, a.qbase + (v - 1) * nc + idx);   // qout may alias qbase: read before the write below
+        }
+      }
+    };
+    if (PRE_ALL && (ld_t || ld_q)) {
+#pragma unroll
+      for (int g0 = 0; g0 < 6; g0 += NV) { start_copies(g0); cp_async_commit(); }
+    }
     // reconstructed quantities in ring order: rho*u_n, p (acoustic pair), then u, v, w, theta -- NV at a time
 #pragma unroll(V0_UNROLL)
     for (int v0 = 0; v0 < 6; v0 += NV) {
-      // start the asynchronous copies of this group's read-modify-write operands; they land while the group is
-      // reconstructed
-      const bool ld_t = upd_on && !a.first, ld_q = upd_on && MODE == 1 && a.a != 0.0;
-#pragma unroll
-      for (int i = 0; i < NV; i++) {
-        const int v = v0 + i, lq = v == 0 ? 0 : v - 1;
-        if (v > 0) {
-          if (ld_t) cp_async8(stg + (2 * i) * MT, a.tend + lq * nc + idx);
-          if (ld_q) cp_async8(stg + (2 * i + 1) * MT, a.qbase + lq * nc + idx);   // qout may alias qbase: read before the write below
-        }
-      }
+      if (!PRE_ALL) start_copies(v0);
       // vertical marches on a shared grid: inlined (uniform per-level table loads are not hoisted out of the cell loop, and
       // without the call the ~100 argument / return moves per cell go away: z march 7.80 -> 7.33 ms). Horizontal marches
       // and member-dependent grids keep the real call (see weno_ring; inlined they spill: measured 7.11 vs 6.78 ms in x,
@@ -281,7 +298,10 @@ k_march_state(const Geom g, const Phys ph, const SweepArgs a) {
       EOn<NV> eo;
       if constexpr (VT == 1 || VT == 3) eo = weno_ring_inl<ORD, NV>(rb + (v0 * ORD) * MT, head, mat);
       else eo = weno_ring<ORD, NV>(rb + (v0 * ORD) * MT, head, mat);
-      if (ld_t || ld_q) cp_async_wait();
+      if (ld_t || ld_q) {
+        if (PRE_ALL) cp_async_wait_left((6 - NV - v0) / NV);     // the later groups may still be in flight
+        else cp_async_wait();
+      }
 #pragma unroll
       for (int i = 0; i < NV; i++) {
         const int v = v0 + i;
@@ -312,7 +332,7 @@ k_march_state(const Geom g, const Phys ph, const SweepArgs a) {
         if (!flux_on) continue;
         if (upd_on) {
           const double div = (F - fpv[l * MT]) * rdd;
-          double T = (ld_t ? stg[(2 * i) * MT] : 0.0) - div;
+          double T = (ld_t ? stg[(2 * (v - 1)) * MT] : 0.0) - div;
           if (MODE == 0) a.tend[l * nc + idx] = T;
           else {
             if (l == idW) T = fma(-gv, rho, T);                 // Dycore.h:560
@@ -321,7 +341,7 @@ k_march_state(const Geom g, const Phys ph, const SweepArgs a) {
             else {
               // round-tripped stage input (x/rho)*rho, Dycore.h:316-319 + :527-530
               const double rt = l == idR ? rho : rb[((RF_U + l - 1) * ORD) * MT + so] * rho;
-              const double o = fma(a.a, ld_q ? stg[(2 * i + 1) * MT] : 0.0, a.b * rt);
+              const double o = fma(a.a, ld_q ? stg[(2 * (v - 1) + 1) * MT] : 0.0, a.b * rt);
               a.qout[l * nc + idx] = fma(a.c, T, o);
             }
           }

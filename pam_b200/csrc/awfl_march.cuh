@@ -269,8 +269,9 @@ k_march_state(const Geom g, const Phys ph, const SweepArgs a) {
     bool up = false;
     // Read-modify-write operands of cell c-1 (partial tendency, step-start state) arrive by asynchronous copies. Where the
     // loop over the variable groups is unrolled (horizontal marches) ALL of them are started here, one commit group per
-    // variable group, and land while the groups are reconstructed; the rolled vertical march starts each group's copies
-    // right before its reconstruction (started here as well it spills 0.8 KB)
+    // variable group, and land while the groups are reconstructed; the rolled vertical march keeps one group ahead (all
+    // started here it spills 0.8 KB; started right before the group's own reconstruction the copies were late: 4 % of the
+    // z march's stall samples, 7.31 -> 7.12 ms)
     constexpr bool PRE_ALL = V0_UNROLL > 1;
     const bool ld_t = upd_on && !a.first, ld_q = upd_on && MODE == 1 && a.a != 0.0;
     auto start_copies = [&](int g0) {
@@ -287,10 +288,11 @@ k_march_state(const Geom g, const Phys ph, const SweepArgs a) {
 #pragma unroll
       for (int g0 = 0; g0 < 6; g0 += NV) { start_copies(g0); cp_async_commit(); }
     }
+    if (!PRE_ALL && (ld_t || ld_q)) { start_copies(0); cp_async_commit(); }
     // reconstructed quantities in ring order: rho*u_n, p (acoustic pair), then u, v, w, theta -- NV at a time
 #pragma unroll(V0_UNROLL)
     for (int v0 = 0; v0 < 6; v0 += NV) {
-      if (!PRE_ALL) start_copies(v0);
+      if (!PRE_ALL && (ld_t || ld_q)) { if (v0 + NV < 6) start_copies(v0 + NV); cp_async_commit(); }   // one group ahead
       // vertical marches on a shared grid: inlined (uniform per-level table loads are not hoisted out of the cell loop, and
       // without the call the ~100 argument / return moves per cell go away: z march 7.80 -> 7.33 ms). Horizontal marches
       // and member-dependent grids keep the real call (see weno_ring; inlined they spill: measured 7.11 vs 6.78 ms in x,
@@ -300,7 +302,7 @@ k_march_state(const Geom g, const Phys ph, const SweepArgs a) {
       else eo = weno_ring<ORD, NV>(rb + (v0 * ORD) * MT, head, mat);
       if (ld_t || ld_q) {
         if (PRE_ALL) cp_async_wait_left((6 - NV - v0) / NV);     // the later groups may still be in flight
-        else cp_async_wait();
+        else cp_async_wait_left(1);                              // all but the group just started
       }
 #pragma unroll
       for (int i = 0; i < NV; i++) {

@@ -198,36 +198,40 @@ __global__ void __launch_bounds__(32, W <= 4 ? 16 : 10) k_fct_update_2d(const Ge
   double *__restrict__ qo = a.qout + (NS + tr) * nc;
   const bool positive = a.positive[tr] != 0;
   // column offsets of the strip, its halo columns (-1, W) and the interface beyond (W+1), periodic in x
-  long off[W + 3];
+  // (32-bit: nx*nens < 2^31 is checked at create; added to a per-level base pointer, one IMAD.WIDE per load instead of
+  // a 64-bit index computation: the kernel spent 30 % of its instructions there)
+  unsigned off[W + 3];
 #pragma unroll
   for (int c = 0; c < W + 3; c++) {
     const int i = ((i0 + c - 1) % g.nx + g.nx) % g.nx;      // once per thread; a ragged last strip can run past the seam
-    off[c] = (long)i * g.nens + e;
+    off[c] = (unsigned)(i * g.nens + e);
   }
   const int kstart = k0 > 0 ? k0 - 1 : 0;
   double A[W + 2], Mp[W], P[W];       // carried: z fluxes of the interface below the level, multipliers and partial result of the level below
   double crdz_prev = 0.0;
 #pragma unroll
   for (int c = 0; c < W + 2; c++) A[c] = __ldg(fz + (long)kstart * sz + off[c]);
+  const double *__restrict__ fxk = fx + (long)kstart * sz, *__restrict__ fzk = fz + (long)(kstart + 1) * sz;
+  const double *__restrict__ qsk = qs + (long)kstart * sz, *q0k = q0 + (long)kstart * sz;
+  double *qok = qo + (long)(kstart - 1) * sz;           // level below the current one
 #pragma unroll
   for (int c = 0; c < W; c++) { Mp[c] = 1.0; P[c] = 0.0; }
 #pragma unroll 1
-  for (int kk = kstart; kk <= k1; kk++) {
+  for (int kk = kstart; kk <= k1; kk++, fxk += sz, fzk += sz, qsk += sz, q0k += sz, qok += sz) {
     const bool inside = kk < g.nz;
-    const long lv = (long)kk * sz;
     double M[W + 2], X[W + 3], B[W + 2], V[W + 2];
     double dzk = 1.0, rdzk = 0.0;
     if (inside) {
       dzk = __ldg(a.dz + (long)kk * g.nens + e); rdzk = __ldg(a.rdz + (long)kk * g.nens + e);
 #pragma unroll
-      for (int c = 0; c < W + 3; c++) X[c] = __ldg(fx + lv + off[c]);
+      for (int c = 0; c < W + 3; c++) X[c] = __ldg(fxk + off[c]);
 #pragma unroll
-      for (int c = 0; c < W + 2; c++) B[c] = __ldg(fz + lv + sz + off[c]);
+      for (int c = 0; c < W + 2; c++) B[c] = __ldg(fzk + off[c]);
 #pragma unroll
-      for (int c = 0; c < W + 2; c++) V[c] = a.b * __ldg(qs + lv + off[c]);
+      for (int c = 0; c < W + 2; c++) V[c] = a.b * __ldg(qsk + off[c]);
       if (a.a != 0.0) {
 #pragma unroll
-        for (int c = 0; c < W + 2; c++) V[c] = fma(a.a, q0[lv + off[c]], V[c]);   // plain load: qout may alias q0
+        for (int c = 0; c < W + 2; c++) V[c] = fma(a.a, q0k[off[c]], V[c]);   // plain load: qout may alias q0
       }
       const double vol = g.dx * g.dy * dzk;
 #pragma unroll
@@ -261,7 +265,7 @@ __global__ void __launch_bounds__(32, W <= 4 ? 16 : 10) k_fct_update_2d(const Ge
       if (finish) {
         double v = fma(-crdz_prev, hA, P[c]);
         if (positive) v = fmax(0.0, v);
-        qo[lv - sz + off[c + 1]] = v;
+        qok[off[c + 1]] = v;
       }
       if (start) {
         const double f0 = fct_scaled(X[c + 1], M[c], M[c + 1], i == 0);

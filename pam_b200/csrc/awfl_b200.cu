@@ -797,10 +797,20 @@ ProfScope::~ProfScope() {
 
 // Segments per line: a power of two (the grid encodes the segment in the low bits of blockIdx.z, see decode_item),
 // chosen so that a segment is about seg_len cells and never shorter than 4.
-static int sbits_for(const awfl_handle *h, int n) {
+static int sbits_for(const awfl_handle *h, int n, int seg_len = 0) {
+  if (seg_len <= 0) seg_len = h->seg_len;
   int sb = 0;
-  while (sb < 4 && (n >> (sb + 1)) >= 4 && (double)n / (1 << sb) > 1.5 * h->seg_len) sb++;
+  while (sb < 4 && (n >> (sb + 1)) >= 4 && (double)n / (1 << sb) > 1.5 * seg_len) sb++;
   return sb;
+}
+// State march: a segment re-reads and re-converts (x^gamma) its halo cells, so whole lines are cheaper as long as there
+// are enough of them to fill the GPU (C2: 6.13 -> 6.04 ms in x, 7.12 -> 7.03 ms in z); a member slab of the host-buffer
+// entry point brings few lines and keeps the shorter segments (e2e 1.17 vs 1.27 G with whole lines). The tracer march has
+// no such conversion and prefers the shorter segments either way (1.18 vs 1.08 ms).
+static int sbits_state(const awfl_handle *h, const Geom &g, int dir, int n) {
+  const long lines = dir == 0 ? (long)g.nz * g.ny : (dir == 1 ? (long)g.nz * g.nx : (long)g.ny * g.nx);
+  const long warps = lines * ((g.ne + 31) / 32);
+  return sbits_for(h, n, warps >= 4096 ? 2 * h->seg_len : h->seg_len);
 }
 static int labits_for(const awfl_handle *h, int dir) {
   const int la = dir == 2 ? h->g.ny : h->g.nz;
@@ -862,10 +872,10 @@ static void run_stage(awfl_handle *h, const Geom &g, const double *qin, const do
     SweepArgs s;
     s.qin = qin; s.qbase = q0; s.qout = mode == 2 ? st_out : qout; s.tend = h->tend; s.mflux = h->mflux[dir];
     s.dz = h->dz; s.grav_var = h->grav_var; s.vtab = h->vtab; s.rdz = h->rdz; s.pcache = h->pcache; s.vst = h->shared_grid ? 1 : g.nens;
-    s.a = a; s.b = b; s.c = b * dt_full; s.first = d == 0; s.sbits = sbits_for(h, nn[dir]); s.labits = labits_for(h, dir);
+    s.a = a; s.b = b; s.c = b * dt_full; s.first = d == 0; s.sbits = sbits_state(h, g, dir, nn[dir]); s.labits = labits_for(h, dir);
     launch_state_sweep(h, g, dir, last ? mode : 0, s);
     TracerSweepArgs t;
-    t.qin = qin; t.mflux = h->mflux[dir]; t.tflux = h->tflux[dir]; t.vtab = h->vtab; t.vst = s.vst; t.sbits = s.sbits; t.labits = s.labits;
+    t.qin = qin; t.mflux = h->mflux[dir]; t.tflux = h->tflux[dir]; t.vtab = h->vtab; t.vst = s.vst; t.sbits = sbits_for(h, nn[dir]); t.labits = s.labits;
     launch_tracer_sweep(h, g, dir, t);
   }
   if (g.nt > 0 && g.sim2d && mode == 1 && !fct_start && h->fused_fct) {

@@ -11,8 +11,11 @@
  *     (pam_core/pam_const.h:30-37, pam_core/pam_coupler.h:255-263) unless a parameter says "host";
  *   - every function returns 0 on success, non-zero on error; awfl_last_error() gives the message
  *     (the reference throws std::string through endrun(), pam_core/pam_const.h:249-252; the shim converts);
- *   - a handle is bound to one device and one stream and is not thread-safe (one coupler per host thread in
- *     the reference, pam_core/pam_interface/pam_interface.h:16-32);
+ *   - a handle is bound to one device and one stream; ONE handle must not be used from two host threads at once,
+ *     but different handles are independent: any number of them may live in one process, on the same or on different
+ *     devices, and be driven from different host threads concurrently (one coupler per host thread in the reference,
+ *     pam_core/pam_interface/pam_interface.h:16-32). Every entry point makes the handle's device current for the
+ *     duration of the call and restores the caller's;
  *   - there is no CPU fallback: every entry point launches sm_100a kernels or fails.
  */
 #ifndef AWFL_B200_H
@@ -139,6 +142,12 @@ double awfl_get_option(const awfl_handle *h, const char *name);
  * (device), ind = 0 left edge / 1 right edge. level < 0: constant horizontal matrices; else the vertical matrices
  * of (level, iens). Static: needs no handle state besides the tables. */
 int awfl_reconstruct(awfl_handle *h, const double *stencils, int n, int ind, int level, int iens, double *out);
+
+/* Where the z marches of this handle read their per-level vertical matrices: 1 = the constant bank of (device, ord),
+ * claimed at awfl_create and shared by handles whose tables are bit-identical; 3 = a global-memory table with unit
+ * stride (shared vertical grid, but the constant bank is held by a handle with another grid, or the table does not fit);
+ * 2 = a member-strided global table (member-dependent grid). Results do not depend on it (same arithmetic). */
+int awfl_table_home(const awfl_handle *h);
 
 /* Number of kernel launches issued by this handle since creation (bench.py reports the per-step count). */
 long awfl_launch_count(const awfl_handle *h);

@@ -16,7 +16,10 @@
 #include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
+#include <map>
+#include <mutex>
 #include <string>
+#include <utility>
 #include <vector>
 
 #include "../../include/awfl_b200.h"
@@ -612,7 +615,6 @@ struct awfl_handle {
   double *tflux[3];      // nt fields each
   double *mult;          // nt fields
   double *dz, *rdz, *grav_var, *vtab, *vs2c, *vwrl, *pint;
-  std::vector<double> vtab_h;   // host copy of the kernel table (constant-bank upload)
   bool use_cvtab;               // shared vertical grid whose table fits the constant bank
   double *dt_min_d, *dt_min_h;   // device scalar + pinned host scalar
   double *mass_d;
@@ -640,10 +642,34 @@ struct awfl_handle {
   double *pcache;        // pressure of the current stage input (SweepArgs::pcache)
 };
 
-static std::string g_create_err;
-// The constant-bank copy of the vertical matrices is per process and per reconstruction order: remember whose it is.
-static const awfl_handle *g_cvtab_owner[4] = {nullptr, nullptr, nullptr, nullptr};
-static int ord_slot(int ord) { return (ord - 3) / 2; }
+// Process-wide state is limited to these two objects. The message of a failed awfl_create is per host thread (one
+// coupler per host thread in the reference, pam_core/pam_interface/pam_interface.h:16-32). The constant-bank copy of the
+// vertical matrices (c_vtab, one per device and reconstruction order) is CLAIMED at awfl_create and kept until
+// awfl_destroy: handles of one (device, order) whose tables are bit-identical share it (reference count); a handle that
+// finds it taken by a different grid reads its own global-memory table instead (MatSel VT 3 / 2). Nothing is uploaded
+// or synchronised inside a time step, so handles on different host threads or devices never race on it.
+static thread_local std::string g_create_err;
+struct CvtabSlot { int refs = 0; std::vector<double> table; };
+static std::mutex g_cvtab_mu;
+static std::map<std::pair<int, int>, CvtabSlot> g_cvtab;   // (device, ord) -> owner table
+
+// Every entry point runs on the handle's device whatever the caller's current device is, and leaves the caller's
+// current device as it found it.
+struct DeviceGuard {
+  int prev = -1, want;
+  cudaError_t err = cudaSuccess;
+  explicit DeviceGuard(int dev) : want(dev) {
+    err = cudaGetDevice(&prev);
+    if (err == cudaSuccess && prev != want) err = cudaSetDevice(want);
+  }
+  ~DeviceGuard() { if (prev >= 0 && prev != want) cudaSetDevice(prev); }
+};
+#define ENTER(h)                                                                                        \
+  DeviceGuard dev_guard_((h)->cfg.device);                                                              \
+  if (dev_guard_.err != cudaSuccess) {                                                                  \
+    (h)->err = std::string("cudaSetDevice: ") + cudaGetErrorString(dev_guard_.err);                     \
+    return 1;                                                                                           \
+  }
 
 #define CK(call)                                                                                        \
   do {                                                                                                  \
@@ -827,24 +853,38 @@ static int labits_for(const awfl_handle *h, int dir) {
     default: OrdLaunch<9>::CALL; break;          \
   }
 
-// Make sure the constant-bank table belongs to this handle before a z march reads it. Another handle of the same
-// order may have replaced it; its kernels may still be running on another stream, so a change of owner synchronises
-// the device first (never happens with one handle per device and order, the normal case).
-static int ensure_cvtab(awfl_handle *h) {
-  if (!h->use_cvtab) return 0;
-  const int slot = ord_slot(h->ord);
-  if (g_cvtab_owner[slot] == h) return 0;
-  if (g_cvtab_owner[slot] != nullptr) CK(cudaDeviceSynchronize());
+// Claim the constant-bank table of (device, order) for this handle (see g_cvtab). Called from awfl_create with the
+// handle's device current. Returns true when the handle may read c_vtab.
+static bool claim_cvtab(awfl_handle *h, const std::vector<double> &vtab) {
+  std::lock_guard<std::mutex> lk(g_cvtab_mu);
+  CvtabSlot &slot = g_cvtab[std::make_pair(h->cfg.device, h->ord)];
+  if (slot.refs > 0) {
+    if (slot.table != vtab) return false;
+    slot.refs++;
+    return true;
+  }
   int rc = 0;
   switch (h->ord) {
-    case 3: rc = OrdLaunch<3>::upload_cvtab(h->stream, h->vtab_h.data(), h->vtab_h.size()); break;
-    case 5: rc = OrdLaunch<5>::upload_cvtab(h->stream, h->vtab_h.data(), h->vtab_h.size()); break;
-    case 7: rc = OrdLaunch<7>::upload_cvtab(h->stream, h->vtab_h.data(), h->vtab_h.size()); break;
-    default: rc = OrdLaunch<9>::upload_cvtab(h->stream, h->vtab_h.data(), h->vtab_h.size()); break;
+    case 3: rc = OrdLaunch<3>::upload_cvtab(vtab.data(), vtab.size()); break;
+    case 5: rc = OrdLaunch<5>::upload_cvtab(vtab.data(), vtab.size()); break;
+    case 7: rc = OrdLaunch<7>::upload_cvtab(vtab.data(), vtab.size()); break;
+    default: rc = OrdLaunch<9>::upload_cvtab(vtab.data(), vtab.size()); break;
   }
-  if (rc != 0) return fail(h, std::string("constant-bank upload of the vertical matrices: ") + cudaGetErrorString((cudaError_t)rc));
-  g_cvtab_owner[slot] = h;
-  return 0;
+  if (rc != 0) return false;
+  slot.table = vtab;
+  slot.refs = 1;
+  return true;
+}
+static void release_cvtab(awfl_handle *h) {
+  if (!h->use_cvtab) return;
+  std::lock_guard<std::mutex> lk(g_cvtab_mu);
+  auto it = g_cvtab.find(std::make_pair(h->cfg.device, h->ord));
+  if (it != g_cvtab.end() && --it->second.refs <= 0) {
+    // the last reader is gone once its kernels have drained; only then may a later handle overwrite the table
+    cudaDeviceSynchronize();
+    g_cvtab.erase(it);
+  }
+  h->use_cvtab = false;
 }
 
 static void launch_state_sweep(awfl_handle *h, const Geom &g, int dir, int mode, const SweepArgs &a) {
@@ -922,6 +962,8 @@ const char *awfl_last_error(const awfl_handle *h) { return h ? h->err.c_str() : 
 
 long awfl_launch_count(const awfl_handle *h) { return h->launches; }
 
+int awfl_table_home(const awfl_handle *h) { return h->use_cvtab ? 1 : (h->shared_grid ? 3 : 2); }
+
 int awfl_create(const awfl_config *cfg, awfl_handle **out) {
   *out = nullptr;
   if (!cfg || cfg->nz < 1 || cfg->ny < 1 || cfg->nx < 1 || cfg->nens < 1 || cfg->num_tracers < 0) { g_create_err = "awfl_create: bad dimensions"; return 1; }
@@ -957,8 +999,12 @@ int awfl_create(const awfl_config *cfg, awfl_handle **out) {
   h->seg_len = 32;
   if (const char *s = getenv("AWFL_SEG_LEN")) { int v = atoi(s); if (v >= 4) h->seg_len = v; }
   auto bail = [&](const std::string &m) { g_create_err = m; awfl_destroy(h); return 1; };
-  cudaError_t ce = cudaSetDevice(cfg->device);
-  if (ce != cudaSuccess) { g_create_err = std::string("cudaSetDevice: ") + cudaGetErrorString(ce) + " (no CPU fallback exists)"; delete h; return 1; }
+  DeviceGuard dev_guard_(cfg->device);
+  if (dev_guard_.err != cudaSuccess) {
+    g_create_err = std::string("cudaSetDevice: ") + cudaGetErrorString(dev_guard_.err) + " (no CPU fallback exists)";
+    delete h;
+    return 1;
+  }
   // NULL = the legacy default stream, which is where the reference (YAKL) enqueues everything and which orders
   // with the caller's own default-stream work (copies, other modules)
   h->own_stream = false;
@@ -974,8 +1020,14 @@ int awfl_create(const awfl_config *cfg, awfl_handle **out) {
   if (getenv("AWFL_FORCE_PER_ENS_GRID")) h->shared_grid = false;
   std::vector<double> vs2c, vwrl, vtab;
   build_vertical(h->ord, g.nz, g.nens, cfg->dz_host, h->shared_grid, vs2c, vwrl, vtab);
-  h->use_cvtab = h->shared_grid && vtab.size() <= OrdLaunch<5>::cvtab_capacity() && !getenv("AWFL_NO_CVTAB");
-  if (h->use_cvtab) h->vtab_h = vtab;
+  // the marching kernels opt in to their shared-memory rings on THIS device (a per-device, per-kernel attribute)
+  switch (h->ord) {
+    case 3: OrdLaunch<3>::configure(); break;
+    case 5: OrdLaunch<5>::configure(); break;
+    case 7: OrdLaunch<7>::configure(); break;
+    default: OrdLaunch<9>::configure(); break;
+  }
+  h->use_cvtab = h->shared_grid && vtab.size() <= OrdLaunch<5>::cvtab_capacity() && !getenv("AWFL_NO_CVTAB") && claim_cvtab(h, vtab);
   const size_t fb = sizeof(double) * (size_t)g.ncell;
   const size_t lvl = sizeof(double) * (size_t)g.ny * g.nx * g.nens;
 #define ALLOC(ptr, bytes) do { if (cudaMalloc((void **)&(ptr), (bytes)) != cudaSuccess) return bail(std::string("cudaMalloc failed for ") + #ptr); } while (0)
@@ -1027,10 +1079,11 @@ int awfl_create(const awfl_config *cfg, awfl_handle **out) {
 
 void awfl_destroy(awfl_handle *h) {
   if (!h) return;
+  DeviceGuard dev_guard_(h->cfg.device);
   for (int b = 0; b < 3; b++) cudaFree(h->Q[b]);
   cudaFree(h->tend);
   for (int d = 0; d < 3; d++) { cudaFree(h->mflux[d]); cudaFree(h->tflux[d]); }
-  for (int o = 0; o < 4; o++) if (g_cvtab_owner[o] == h) g_cvtab_owner[o] = nullptr;
+  release_cvtab(h);
   cudaFree(h->mult); cudaFree(h->dz); cudaFree(h->rdz); cudaFree(h->grav_var); cudaFree(h->vtab); cudaFree(h->vs2c); cudaFree(h->vwrl);
   cudaFree(h->pint); cudaFree(h->dt_min_d); cudaFree(h->mass_d); cudaFree(h->positive_d); cudaFree(h->adds_mass_d);
   cudaFree(h->pcache); cudaFree(h->trptr_d); cudaFree(h->trptr_out_d); cudaFree(h->stage_fields); cudaFree(h->stage_out); cudaFree(h->tmp_state);
@@ -1078,6 +1131,7 @@ int awfl_current_device(void) {
 }
 
 int awfl_set_variable_gravity(awfl_handle *h, const double *variable_gravity) {
+  ENTER(h);
   if (!variable_gravity) return fail(h, "awfl_set_variable_gravity: NULL pointer");
   if (variable_gravity == h->grav_var) return 0;
   CK(cudaMemcpyAsync(h->grav_var, variable_gravity, sizeof(double) * h->g.nz * h->g.nens, cudaMemcpyDeviceToDevice, h->stream));
@@ -1085,6 +1139,7 @@ int awfl_set_variable_gravity(awfl_handle *h, const double *variable_gravity) {
 }
 
 int awfl_export_tables(awfl_handle *h, double *variable_gravity, double *vert_sten_to_coefs, double *vert_weno_recon_lower) {
+  ENTER(h);
   const Geom &g = h->g;
   const size_t o = h->ord, hs = h->hs, lv = (size_t)(g.nz + 2) * g.nens;
   if (variable_gravity) CK(cudaMemcpyAsync(variable_gravity, h->grav_var, sizeof(double) * g.nz * g.nens, cudaMemcpyDeviceToDevice, h->stream));
@@ -1094,6 +1149,7 @@ int awfl_export_tables(awfl_handle *h, double *variable_gravity, double *vert_st
 }
 
 int awfl_compute_time_step(awfl_handle *h, const awfl_fields *f, double cfl, double *dt_host) {
+  ENTER(h);
   FieldPtrs fp;
   if (make_field_ptrs(h, f, fp)) return 1;
   const double inf = INFINITY;
@@ -1151,6 +1207,7 @@ static void step_convert_out(awfl_handle *h, const Geom &g, const FieldPtrs &fp,
 }
 
 int awfl_time_step(awfl_handle *h, const awfl_fields *f, double crm_dt, int ncycles_override, int *ncycles_out) {
+  ENTER(h);
   if (!(crm_dt > 0.0)) return fail(h, "awfl_time_step: crm_dt must be positive");
   FieldPtrs fp;
   if (make_field_ptrs(h, f, fp)) return 1;
@@ -1164,7 +1221,6 @@ int awfl_time_step(awfl_handle *h, const awfl_fields *f, double crm_dt, int ncyc
   int ncycles = ncycles_override;
   if (need_dt && step_ncycles(h, crm_dt, &ncycles)) return 1;
   const double dt = crm_dt / ncycles;       // Dycore.h:145
-  if (ensure_cvtab(h)) return 1;
   const int qi = step_advance(h, g, ncycles, dt);
   step_convert_out(h, g, fp, qi);
   CK(cudaGetLastError());
@@ -1211,6 +1267,7 @@ int awfl_host_slabs(const awfl_handle *h) { return host_slab_count(h); }
 // prediction (first call) the slabs wait for the dt.
 // Results are identical to awfl_time_step on the same fields for any slab count (members never interact).
 int awfl_time_step_host(awfl_handle *h, double *const *host_fields, double crm_dt, int ncycles_override, int *ncycles_out) {
+  ENTER(h);
   if (!(crm_dt > 0.0)) return fail(h, "awfl_time_step_host: crm_dt must be positive");
   // AWFL_HOST_TRACE=1: device timeline of this call on stderr (timing events on the three streams; diagnostic only)
   static const bool trace = getenv("AWFL_HOST_TRACE") && atoi(getenv("AWFL_HOST_TRACE")) > 0;
@@ -1256,7 +1313,6 @@ int awfl_time_step_host(awfl_handle *h, double *const *host_fields, double crm_d
     const double inf = INFINITY;
     CK(cudaMemcpyAsync(h->dt_min_d, &inf, sizeof(double), cudaMemcpyHostToDevice, h->stream));
   }
-  if (ensure_cvtab(h)) return 1;
   // the copy streams must not run ahead of earlier work on the compute stream (staging buffers, tracer pointer tables,
   // dt reset)
   CK(cudaEventRecord(h->slab_ev[2 * P], h->stream));
@@ -1356,12 +1412,12 @@ long awfl_host_mispredictions(const awfl_handle *h) { return h->host_mispredicti
 
 int awfl_compute_tendencies(awfl_handle *h, const double *state, const double *tracers, const double *fct_start, double dt,
                             double *state_tend, double *tracers_tend) {
+  ENTER(h);
   const Geom &g = h->g;
   const size_t fb = sizeof(double) * (size_t)g.ncell;
   // gather (state | tracers) into one N-field buffer
   CK(cudaMemcpyAsync(h->Q[1], state, fb * NS, cudaMemcpyDeviceToDevice, h->stream));
   if (g.nt > 0) CK(cudaMemcpyAsync(h->Q[1] + (size_t)NS * g.ncell, tracers, fb * g.nt, cudaMemcpyDeviceToDevice, h->stream));
-  if (ensure_cvtab(h)) return 1;
   run_stage(h, h->g, h->Q[1], h->Q[1], nullptr, 0.0, 1.0, dt, dt, 1.0, 0.0, 2, fct_start, state_tend, tracers_tend);
   CK(cudaGetLastError());
   CK(cudaStreamSynchronize(h->stream));
@@ -1369,6 +1425,7 @@ int awfl_compute_tendencies(awfl_handle *h, const double *state, const double *t
 }
 
 int awfl_declare_hydrostatic(awfl_handle *h, const awfl_fields *f, const awfl_gcm_columns *gcm) {
+  ENTER(h);
   const Geom &g = h->g;
   HydroArgs a;
   memset(&a, 0, sizeof(a));
@@ -1395,6 +1452,7 @@ int awfl_declare_hydrostatic(awfl_handle *h, const awfl_fields *f, const awfl_gc
 }
 
 int awfl_init_idealized(awfl_handle *h, const awfl_fields *f, const double *zint, int data_spec) {
+  ENTER(h);
   if (data_spec != 0 && data_spec != 1) return fail(h, "awfl_init_idealized: data_spec must be 0 (thermal) or 1 (supercell)");
   if (!zint) return fail(h, "awfl_init_idealized: vertical_interface_height is required");
   const Geom &g = h->g;
@@ -1419,6 +1477,7 @@ int awfl_init_idealized(awfl_handle *h, const awfl_fields *f, const double *zint
 }
 
 int awfl_compute_mass(awfl_handle *h, const awfl_fields *f, double *out_host) {
+  ENTER(h);
   const Geom &g = h->g;
   FieldPtrs fp;
   if (make_field_ptrs(h, f, fp)) return 1;
@@ -1434,6 +1493,7 @@ int awfl_compute_mass(awfl_handle *h, const awfl_fields *f, double *out_host) {
 }
 
 int awfl_reconstruct(awfl_handle *h, const double *stencils, int n, int ind, int level, int iens, double *out) {
+  ENTER(h);
   if (level >= h->g.nz + 2 || iens < 0 || iens >= h->g.nens) return fail(h, "awfl_reconstruct: level/iens out of range");
   AWFL_ORD_DISPATCH(reconstruct(h->stream, stencils, n, ind, level, iens, h->g.nens, h->vtab, h->shared_grid, out));
   h->launches++;
@@ -1448,6 +1508,7 @@ int awfl_profile_begin(awfl_handle *h) {
 }
 
 int awfl_profile_end(awfl_handle *h, double *ms_by_class, long *launches_by_class) {
+  ENTER(h);
   h->prof = false;
   CK(cudaStreamSynchronize(h->stream));
   for (int c = 0; c < KC_COUNT; c++) { ms_by_class[c] = 0.0; launches_by_class[c] = 0; }
@@ -1462,6 +1523,7 @@ int awfl_profile_end(awfl_handle *h, double *ms_by_class, long *launches_by_clas
 }
 
 int awfl_measure_fp64_peak(awfl_handle *h, int iters, double *tflops) {
+  ENTER(h);
   int dev = 0, sms = 0;
   CK(cudaGetDevice(&dev));
   CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));

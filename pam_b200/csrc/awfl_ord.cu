@@ -1,6 +1,5 @@
 // One translation unit per reconstruction order (-DAWFL_ORD_INST=3|5|7|9): instantiates the order-templated kernels of
 // awfl_sweep.cuh and defines the host launchers declared in awfl_types.h.
-#include <set>
 #include "awfl_sweep.cuh"
 #include "awfl_march.cuh"
 
@@ -10,16 +9,17 @@
 
 namespace awfl {
 
-// Launch a marching kernel with its dynamic shared-memory ring; the first launch of each kernel opts in to > 48 KB of
-// dynamic shared memory and asks for the largest shared-memory carve-out.
+// A marching kernel and its dynamic shared-memory ring. The opt-in to > 48 KB of dynamic shared memory and the request
+// for the largest shared-memory carve-out are per device and per kernel: OrdLaunch<ORD>::configure() sets them for every
+// instantiation when a handle is created on a device (no lazily filled process-wide set: handles on several devices or
+// host threads share nothing).
+template <class... KArgs>
+static void configure_march(void (*kernel)(KArgs...), size_t bytes) {
+  cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+  cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+}
 template <class... KArgs, class... Args>
 static void launch_march(void (*kernel)(KArgs...), dim3 blocks, size_t bytes, cudaStream_t s, const Args &...args) {
-  static std::set<const void *> configured;
-  if (!configured.count((const void *)kernel)) {
-    cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
-    cudaFuncSetAttribute(kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
-    configured.insert((const void *)kernel);
-  }
   kernel<<<blocks, MT, bytes, s>>>(args...);
 }
 #define AWFL_LAUNCH_MARCH(KERNEL, BYTES, ...) launch_march(KERNEL, blocks, BYTES, s, __VA_ARGS__)
@@ -62,9 +62,26 @@ void OrdLaunch<ORD>::march_tracer(cudaStream_t s, const Geom &g, const TracerSwe
 }
 
 template <int ORD>
-int OrdLaunch<ORD>::upload_cvtab(cudaStream_t s, const double *host, size_t ndoubles) {
+void OrdLaunch<ORD>::configure() {
+  constexpr size_t BS = MarchCfg<ORD>::SMEM_STATE, BT = MarchCfg<ORD>::SMEM_TRACER;
+  configure_march(k_march_state<ORD, 0, 0, 0>, BS);
+  configure_march(k_march_state<ORD, 1, 0, 0>, BS);
+  configure_march(k_march_state<ORD, 2, 1, 1>, BS);
+  configure_march(k_march_state<ORD, 2, 1, 2>, BS);
+  configure_march(k_march_state<ORD, 2, 1, 3>, BS);
+  configure_march(k_march_state<ORD, 2, 2, 1>, BS);
+  configure_march(k_march_state<ORD, 2, 2, 2>, BS);
+  configure_march(k_march_tracer<ORD, 0, 0>, BT);
+  configure_march(k_march_tracer<ORD, 1, 0>, BT);
+  configure_march(k_march_tracer<ORD, 2, 1>, BT);
+  configure_march(k_march_tracer<ORD, 2, 2>, BT);
+  configure_march(k_march_tracer<ORD, 2, 3>, BT);
+}
+
+template <int ORD>
+int OrdLaunch<ORD>::upload_cvtab(const double *host, size_t ndoubles) {
   if (ndoubles > (size_t)AWFL_CVTAB_DOUBLES) return (int)cudaErrorInvalidValue;
-  return (int)cudaMemcpyToSymbolAsync(c_vtab, host, ndoubles * sizeof(double), 0, cudaMemcpyHostToDevice, s);
+  return (int)cudaMemcpyToSymbol(c_vtab, host, ndoubles * sizeof(double), 0, cudaMemcpyHostToDevice);
 }
 
 template <int ORD>

@@ -63,7 +63,8 @@ template <int ORD> struct OrdLaunch {
   // cell-centred marching kernels (awfl_march.cuh); vt: 0 constant horizontal, 1 constant-bank vertical, 2 global vertical
   static void march_state(cudaStream_t s, const Geom &g, const Phys &ph, const SweepArgs &a, int dir, int mode, int vt);
   static void march_tracer(cudaStream_t s, const Geom &g, const TracerSweepArgs &a, int dir, int vt);
-  static int upload_cvtab(cudaStream_t s, const double *host, size_t ndoubles);   // returns a cudaError_t
+  static void configure();   // per-device kernel attributes (shared-memory rings) of every marching kernel of this order
+  static int upload_cvtab(const double *host, size_t ndoubles);   // synchronous; returns a cudaError_t
   static size_t cvtab_capacity();
   static void hydro_pint(cudaStream_t s, const Geom &g, const Phys &ph, const HydroArgs &a, bool shared);
   static void reconstruct(cudaStream_t s, const double *st, int n, int ind, int level, int iens, int nens, const double *vtab, bool shared, double *out);

@@ -238,6 +238,10 @@ class Dycore:
         """Slab count the next time_step_host will use (0 passed to set_host_slabs = chosen from the grid)."""
         return int(self.lib.awfl_host_slabs(self.h))
 
+    def table_home(self):
+        """1: vertical matrices in the constant bank, 3: unit-stride global table, 2: member-strided global table."""
+        return int(self.lib.awfl_table_home(self.h))
+
     def host_mispredictions(self):
         """Calls of time_step_host whose predicted sub-cycle count was wrong (redone un-overlapped)."""
         return self.lib.awfl_host_mispredictions(self.h)

@@ -285,3 +285,110 @@ def test_errors_are_reported_not_swallowed():
         Dycore(5).init(c)
     with pytest.raises(RuntimeError):
         Dycore(4)
+
+
+def _steps(case, ord, nsteps, device="cuda:0"):
+    c, d = H.make_gpu(case, ord, crm_dt=2.0, device=device)
+    d.declare_current_profile_as_hydrostatic(c)
+    for _ in range(nsteps):
+        d.timeStep(c)
+    out = H.gpu_fields(c)
+    home = d.table_home()
+    d.finalize()
+    return out, home
+
+
+def test_two_handles_of_one_order_with_different_grids_interleave():
+    """The MMF process model (pam_interface.h:16-32: one coupler per host thread) puts several handles of one order on
+    one device. The constant-bank copy of the vertical matrices belongs to the first; a second handle with ANOTHER
+    vertical grid reads its own global table, one with the SAME grid shares the constant bank. Stepped alternately, every
+    handle must give the bits it gives alone, and no step may re-upload or synchronise anything."""
+    a = _case(nz=14, nx=10, nens=40, grid="tanh")
+    b = _case(nz=14, nx=10, nens=40, grid="equal", seed=777)
+    ref_a, home_a = _steps(a, 5, 3)
+    ref_b, home_b = _steps(b, 5, 3)
+    assert home_a == 1 and home_b == 1            # alone, each owns the constant bank
+    ca, da = H.make_gpu(a, 5, crm_dt=2.0)
+    cb, db = H.make_gpu(b, 5, crm_dt=2.0)
+    ca2, da2 = H.make_gpu(a, 5, crm_dt=2.0)
+    assert (da.table_home(), db.table_home(), da2.table_home()) == (1, 3, 1)
+    for c, d in ((ca, da), (cb, db), (ca2, da2)):
+        d.declare_current_profile_as_hydrostatic(c)
+    for _ in range(3):
+        da.timeStep(ca); db.timeStep(cb); da2.timeStep(ca2)
+    for ref, c in ((ref_a, ca), (ref_b, cb), (ref_a, ca2)):
+        got = H.gpu_fields(c)
+        for k in ref:
+            assert np.array_equal(got[k], ref[k]), k
+    # the owner goes away: the bank is released only when its last reader does
+    da.finalize()
+    cc, dc = H.make_gpu(b, 5, crm_dt=2.0)
+    assert dc.table_home() == 3
+    da2.finalize(); dc.finalize(); db.finalize()
+    cd, dd = H.make_gpu(b, 5, crm_dt=2.0)
+    assert dd.table_home() == 1
+
+
+def test_handles_on_two_host_threads_run_concurrently():
+    """Two host threads, each with its own coupler + handle (different grids, same order, same device, own streams),
+    stepping at the same time: bits equal to the single-handle runs."""
+    import threading
+    import torch
+    cases = [_case(nz=14, nx=10, nens=40, grid="tanh"), _case(nz=14, nx=10, nens=40, grid="equal", seed=777)]
+    refs = [_steps(cs, 5, 6)[0] for cs in cases]
+    out, err = [None, None], []
+
+    def work(i):
+        try:
+            with torch.cuda.stream(torch.cuda.Stream("cuda:0")):
+                c, d = H.make_gpu(cases[i], 5, crm_dt=2.0)
+                d.declare_current_profile_as_hydrostatic(c)
+                for _ in range(6):
+                    d.timeStep(c)
+                torch.cuda.current_stream().synchronize()
+                out[i] = H.gpu_fields(c)
+                d.finalize()
+        except Exception as ex:      # surfaced below
+            err.append(ex)
+
+    th = [threading.Thread(target=work, args=(i,)) for i in range(2)]
+    for t in th:
+        t.start()
+    for t in th:
+        t.join()
+    assert not err, err
+    for i in range(2):
+        for k in refs[i]:
+            assert np.array_equal(out[i][k], refs[i][k]), (i, k)
+
+
+def test_two_devices_in_one_process_and_parity_of_each_shard():
+    """One process driving two GPUs: every entry point runs on its handle's device whatever the
+    current device is. Two member shards of one ensemble (pam_b200.parallel.shard_range) are stepped on cuda:0 and cuda:1
+    through the CUDA path and EACH is compared with the oracle (<= 1e-12), the multi-GPU form of the one-step parity
+    test. Skipped below two visible devices."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two visible CUDA devices")
+    from pam_b200.parallel import shard_range
+    full = _case(nz=14, nx=12, nens=70)
+    o = H.make_oracle(full, 5, crm_dt=2.0)
+    o.declare_hydrostatic()
+    o.time_step()
+    ref = o.get_fields()
+    fl = field_floors(ref)
+    torch.cuda.set_device(0)
+    for rank in range(2):
+        e0, e1 = shard_range(70, rank, 2)
+        shard = dict(full)
+        shard["nens"] = e1 - e0
+        shard["fields"] = {k: np.ascontiguousarray(v[..., e0:e1]) for k, v in full["fields"].items()}
+        c, d = H.make_gpu(shard, 5, crm_dt=2.0, device="cuda:%d" % rank)     # current device stays 0 for both
+        d.declare_current_profile_as_hydrostatic(c)
+        d.timeStep(c)
+        got = H.gpu_fields(c)
+        for k in ref:
+            r = ref[k][..., e0:e1]
+            assert rel_l2(got[k], r, fl[k]) <= TOL_STEP, (rank, k)
+        d.finalize()
+    assert torch.cuda.current_device() == 0

@@ -98,6 +98,40 @@ int awfl_compute_time_step(awfl_handle *h, const awfl_fields *f, double cfl, dou
 int awfl_compute_tendencies(awfl_handle *h, const double *state, const double *tracers, const double *fct_start,
                             double dt, double *state_tend, double *tracers_tend);
 
+/* ---- The reference's HALOED dynamics arrays (the arguments of the other public Dycore methods) ----
+ * state   (5, nz+2hs, ny+2hs, nx+2hs, nens) = rho, rho*u, rho*v, rho*w, rho*theta     hs = (ord+1)/2
+ * tracers (num_tracers, nz+2hs, ny+2hs, nx+2hs, nens)
+ * pressure (nz+2hs, ny+2hs, nx+2hs, nens);  state_tend (5,nz,ny,nx,nens), tracers_tend (num_tracers,nz,ny,nx,nens)
+ * All DEVICE pointers, C order, nens fastest -- the layout of the reference's real5d / real4d arrays. The time step
+ * itself never builds these arrays; the entry points below give a caller who holds them the reference's methods with
+ * the reference's effects on that memory. Work is enqueued on the handle's stream (no host synchronisation). */
+
+/* Dycore::convert_coupler_to_dynamics (Dycore.h:1336-1388): coupler fields -> interior of state / tracers. */
+int awfl_convert_coupler_to_dynamics(awfl_handle *h, const awfl_fields *f, double *state, double *tracers);
+
+/* Dycore::convert_dynamics_to_coupler (Dycore.h:1281-1331): interior of state / tracers -> coupler fields. */
+int awfl_convert_dynamics_to_coupler(awfl_handle *h, const double *state, const double *tracers, const awfl_fields *f);
+
+/* Dycore::halo_exchange (Dycore.h:608-711) on arrays whose velocities, theta and tracers are already divided by density:
+ * periodic x (and, in 3-D, y) ghosts, wall ghosts in z (w = 0, the others zero-gradient, density by hydrostatic
+ * extrapolation at constant theta, pressure from it). Ghost theta is the boundary cell's (the intended value where the
+ * reference has a read/write race). Corner ghosts are not touched, as in the reference. */
+int awfl_halo_exchange(awfl_handle *h, double *state, double *tracers, double *pressure);
+
+/* Dycore::compute_tendencies (Dycore.h:262-586) with the reference's own signature: tracers_tend holds the FCT start
+ * mass on entry (Dycore.h:158,173,197) and the tracer tendencies on return; state / tracers come back as the reference
+ * leaves them -- interior divided by density and multiplied back ((x/rho)*rho, Dycore.h:316-320,527-532: the SSPRK3
+ * update consumes exactly that), ghosts filled as by halo_exchange. Uses the handle's variable_gravity. */
+int awfl_compute_tendencies_haloed(awfl_handle *h, double *state, double *state_tend, double *tracers, double *tracers_tend, double dt);
+
+/* Dycore::compute_mass (Dycore.h:37-60) with the reference's arguments: out_device (num_tracers+2, nens) DEVICE array
+ * (the reference returns a device real2d). */
+int awfl_compute_mass_dynamics(awfl_handle *h, const double *state, const double *tracers, double *out_device);
+
+/* Dycore::init_supercell (Dycore.h:1096-1276): the supercell sounding as interior values of state / tracers.
+ * zint: DEVICE "vertical_interface_height" (nz+1,nens). Init-time call: allocates scratch and synchronises. */
+int awfl_init_supercell(awfl_handle *h, double *state, double *tracers, const double *zint);
+
 /* Dycore::declare_current_profile_as_hydrostatic (Dycore.h:1392-1504), grav_balance branch: fills the handle's
  * "variable_gravity" (nz,nens). gcm == NULL <=> use_gcm_data == false. Deterministic (no atomics). */
 int awfl_declare_hydrostatic(awfl_handle *h, const awfl_fields *f, const awfl_gcm_columns *gcm);

@@ -9,7 +9,7 @@
  *
  * PARITY PINNING: the reference has no golden vectors for this path, so this oracle is
  * pinned against the reference ITSELF, compiled unmodified in oracle/_ref (oracle/ref_build): tests/
- * test_oracle_vs_ref.py requires bit-identical tables, reconstructions, tendencies and time steps, and
+ * test_oracle_golden.py requires bit-identical tables, reconstructions, tendencies and time steps, and
  * tests/golden/ holds outputs of the compiled reference for the GPU box.
  *
  * Semantics: the reference's bottom boundary condition has a read/write ordering hazard (Dycore.h:670 vs
@@ -792,5 +792,44 @@ int orc_compute_mass(void *h, double *const *f, double *out) {
       out[v * o->nens + e] = s / ((double)o->nz * o->ny * o->nx);
     }
   free(q); free(tr);
+  return 0;
+}
+
+/* ------------------------------------------------------------------------------------------------ */
+/* The reference's public methods on its HALOED arrays (Dycore.h:37, :262, :608, :1281, :1336), for the */
+/* parity tests of the C ABI's awfl_*_haloed / awfl_convert_* / awfl_halo_exchange entry points.        */
+/* st (5,nz+2hs,ny+2hs,nx+2hs,nens), tr (nt,...), pr (nz+2hs,ny+2hs,nx+2hs,nens), caller-owned.         */
+/* ------------------------------------------------------------------------------------------------ */
+void orc_halo_shape(void *h, int *dims) { orc_t *o = (orc_t *)h; dims[0] = NZH; dims[1] = NYH; dims[2] = NXH; }
+int orc_halo_exchange(void *h, double *st, double *tr, double *pr) { halo_exchange((orc_t *)h, st, tr, pr); return 0; }
+int orc_compute_tendencies_haloed(void *h, double *st, double *st_tend, double *tr, double *tr_tend, double dt) {
+  compute_tendencies((orc_t *)h, st, st_tend, tr, tr_tend, dt);
+  return 0;
+}
+int orc_convert_coupler_to_dynamics(void *h, double *const *f, double *st, double *tr) {
+  coupler_to_dynamics((orc_t *)h, f, st, tr);
+  return 0;
+}
+int orc_convert_dynamics_to_coupler(void *h, const double *st, const double *tr, double *const *f) {
+  dynamics_to_coupler((orc_t *)h, st, tr, f);
+  return 0;
+}
+/* Dycore.h:37-60 with the reference's arguments */
+int orc_compute_mass_dynamics(void *h, const double *q, const double *tr, double *out) {
+  orc_t *o = (orc_t *)h;
+  int nt = o->nt;
+  size_t nh = halo_count(o);
+  for (int v = 0; v < nt + 2; v++)
+    for (int e = 0; e < o->nens; e++) {
+      double s = 0;
+      for (int k = 0; k < o->nz; k++)
+        for (int j = 0; j < o->ny; j++)
+          for (int i = 0; i < o->nx; i++) {
+            size_t hh = H4(HS + k, HS + j, HS + i, e);
+            double val = v < nt ? tr[(size_t)v * nh + hh] : (v == nt ? q[idR * nh + hh] : q[idT * nh + hh]);
+            s += val * o->dz[k * o->nens + e];
+          }
+      out[v * o->nens + e] = s / ((double)o->nz * o->ny * o->nx);
+    }
   return 0;
 }

@@ -63,6 +63,13 @@ def load(ord=5):
     lib.orc_time_step.argtypes = [C.c_void_p, _dpp, C.c_double, C.c_int]
     lib.orc_declare_hydrostatic.argtypes = [C.c_void_p, _dpp, _dpp]
     lib.orc_compute_mass.argtypes = [C.c_void_p, _dpp, _dp]
+    lib.orc_halo_shape.argtypes = [C.c_void_p, C.POINTER(C.c_int)]
+    lib.orc_halo_shape.restype = None
+    lib.orc_halo_exchange.argtypes = [C.c_void_p, _dp, _dp, _dp]
+    lib.orc_compute_tendencies_haloed.argtypes = [C.c_void_p, _dp, _dp, _dp, _dp, C.c_double]
+    lib.orc_convert_coupler_to_dynamics.argtypes = [C.c_void_p, _dpp, _dp, _dp]
+    lib.orc_convert_dynamics_to_coupler.argtypes = [C.c_void_p, _dp, _dp, _dpp]
+    lib.orc_compute_mass_dynamics.argtypes = [C.c_void_p, _dp, _dp, _dp]
     _libs[ord] = lib
     return lib
 
@@ -209,4 +216,29 @@ class OracleDycore:
     def compute_mass(self):
         out = np.empty((self.nt + 2, self.nens))
         assert self.lib.orc_compute_mass(self.h, self._fptrs(), _p(out)) == 0
+        return out
+
+    # ---- the reference's public methods on its HALOED arrays (Dycore.h:37,262,608,1281,1336); arrays are modified in place ----
+    def halo_shape(self):
+        hs = self.hs
+        return (self.nz + 2 * hs, self.ny + 2 * hs, self.nx + 2 * hs, self.nens)
+
+    def halo_exchange(self, state, tracers, pressure):
+        assert self.lib.orc_halo_exchange(self.h, _p(state), _p(tracers), _p(pressure)) == 0
+
+    def compute_tendencies_haloed(self, state, tracers, tracers_tend, dt):
+        """state / tracers (haloed) and tracers_tend (FCT start mass in, tendencies out) are modified in place; returns state_tend."""
+        st = np.empty((5,) + self.shape4)
+        assert self.lib.orc_compute_tendencies_haloed(self.h, _p(state), _p(st), _p(tracers), _p(tracers_tend), float(dt)) == 0
+        return st
+
+    def convert_coupler_to_dynamics(self, state, tracers):
+        assert self.lib.orc_convert_coupler_to_dynamics(self.h, self._fptrs(), _p(state), _p(tracers)) == 0
+
+    def convert_dynamics_to_coupler(self, state, tracers):
+        assert self.lib.orc_convert_dynamics_to_coupler(self.h, _p(state), _p(tracers), self._fptrs()) == 0
+
+    def compute_mass_dynamics(self, state, tracers):
+        out = np.empty((self.nt + 2, self.nens))
+        assert self.lib.orc_compute_mass_dynamics(self.h, _p(state), _p(tracers), _p(out)) == 0
         return out

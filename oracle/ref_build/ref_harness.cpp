@@ -69,6 +69,9 @@ void prefill_bottom_ghost_theta(Handle &h, real5d const &state) {
   }
 }
 
+template <class A> void fill_from(A &a, const double *src) { std::memcpy(a.data(), src, a.size()*sizeof(double)); }
+template <class A> void copy_to  (A const &a, double *dst) { std::memcpy(dst, a.data(), a.size()*sizeof(double)); }
+
 void tend_intended(Handle &h, real5d const &state, real5d const &state_tend,
                    real5d const &tracers, real5d const &tracers_tend, real dt) {
   prefill_bottom_ghost_theta(h, state);
@@ -563,6 +566,82 @@ double ref_time_steps_raw(void *hv, int nsteps) {
   yakl::fence();
   auto t1 = std::chrono::steady_clock::now();
   return std::chrono::duration<double>(t1-t0).count();
+}
+
+// ---------------------------------------------------------------------------------------------------
+// The reference's public methods on caller-owned HALOED arrays, flattened C order (pins the oracle's
+// orc_*_haloed / orc_convert_* / orc_halo_exchange, which in turn check the C ABI's entry points).
+// ---------------------------------------------------------------------------------------------------
+int ref_halo_exchange(void *hv, double *st, double *tr, double *pr) {
+  Handle &h = *(Handle*)hv;
+  int nz=h.nz, ny=h.ny, nx=h.nx, nens=h.nens, nt=h.nt;
+  real5d state  ("state"  ,5 ,nz+2*HS,ny+2*HS,nx+2*HS,nens);
+  real5d tracers("tracers",nt,nz+2*HS,ny+2*HS,nx+2*HS,nens);
+  real4d pressure("pressure",nz+2*HS,ny+2*HS,nx+2*HS,nens);
+  fill_from(state, st); if (nt>0) fill_from(tracers, tr); fill_from(pressure, pr);
+  // F2: the bottom ghost theta the racing thread would have written (here the array already holds theta)
+  for (int kk=0; kk<HS; kk++) for (int j=0;j<ny;j++) for (int i=0;i<nx;i++) for (int e=0;e<nens;e++)
+    state(idT,kk,HS+j,HS+i,e) = state(idT,HS,HS+j,HS+i,e);
+  try { h.dycore.halo_exchange(h.coupler, state, tracers, pressure); } catch (...) { return 1; }
+  copy_to(state, st); if (nt>0) copy_to(tracers, tr); copy_to(pressure, pr);
+  return 0;
+}
+int ref_compute_tendencies_haloed(void *hv, double *st, double *st_tend, double *tr, double *tr_tend, double dt) {
+  Handle &h = *(Handle*)hv;
+  int nz=h.nz, ny=h.ny, nx=h.nx, nens=h.nens, nt=h.nt;
+  real5d state  ("state"  ,5 ,nz+2*HS,ny+2*HS,nx+2*HS,nens);
+  real5d tracers("tracers",nt,nz+2*HS,ny+2*HS,nx+2*HS,nens);
+  real5d state_tend  ("state_tend"  ,5 ,nz,ny,nx,nens);
+  real5d tracers_tend("tracers_tend",nt,nz,ny,nx,nens);
+  fill_from(state, st); if (nt>0) { fill_from(tracers, tr); fill_from(tracers_tend, tr_tend); }
+  try { tend_intended(h, state, state_tend, tracers, tracers_tend, dt); } catch (...) { return 1; }
+  copy_to(state, st); copy_to(state_tend, st_tend);
+  if (nt>0) { copy_to(tracers, tr); copy_to(tracers_tend, tr_tend); }
+  return 0;
+}
+int ref_convert_coupler_to_dynamics(void *hv, double *st, double *tr) {
+  Handle &h = *(Handle*)hv;
+  int nz=h.nz, ny=h.ny, nx=h.nx, nens=h.nens, nt=h.nt;
+  real5d state  ("state"  ,5 ,nz+2*HS,ny+2*HS,nx+2*HS,nens);
+  real5d tracers("tracers",nt,nz+2*HS,ny+2*HS,nx+2*HS,nens);
+  fill_from(state, st); if (nt>0) fill_from(tracers, tr);
+  try { h.dycore.convert_coupler_to_dynamics(h.coupler, state, tracers); } catch (...) { return 1; }
+  copy_to(state, st); if (nt>0) copy_to(tracers, tr);
+  return 0;
+}
+int ref_convert_dynamics_to_coupler(void *hv, const double *st, const double *tr) {
+  Handle &h = *(Handle*)hv;
+  int nz=h.nz, ny=h.ny, nx=h.nx, nens=h.nens, nt=h.nt;
+  real5d state  ("state"  ,5 ,nz+2*HS,ny+2*HS,nx+2*HS,nens);
+  real5d tracers("tracers",nt,nz+2*HS,ny+2*HS,nx+2*HS,nens);
+  fill_from(state, st); if (nt>0) fill_from(tracers, tr);
+  try { h.dycore.convert_dynamics_to_coupler(h.coupler, state, tracers); } catch (...) { return 1; }
+  return 0;
+}
+int ref_compute_mass_dynamics(void *hv, const double *st, const double *tr, double *out) {
+  Handle &h = *(Handle*)hv;
+  int nz=h.nz, ny=h.ny, nx=h.nx, nens=h.nens, nt=h.nt;
+  real5d state  ("state"  ,5 ,nz+2*HS,ny+2*HS,nx+2*HS,nens);
+  real5d tracers("tracers",nt,nz+2*HS,ny+2*HS,nx+2*HS,nens);
+  fill_from(state, st); if (nt>0) fill_from(tracers, tr);
+  try {
+    auto m = h.dycore.compute_mass(h.coupler, state, tracers);
+    std::memcpy(out, m.data(), (size_t)(nt+2)*nens*sizeof(double));
+  } catch (...) { return 1; }
+  return 0;
+}
+// Dycore::init_supercell proper: the haloed arrays it fills (interior), flattened
+int ref_init_supercell_dynamics(void *hv, double *st, double *tr) {
+  Handle &h = *(Handle*)hv;
+  int nz=h.nz, ny=h.ny, nx=h.nx, nens=h.nens, nt=h.nt;
+  try {
+    real5d state  ("state"  ,5 ,nz+2*HS,ny+2*HS,nx+2*HS,nens);
+    real5d tracers("tracers",nt,nz+2*HS,ny+2*HS,nx+2*HS,nens);
+    state = 0; tracers = 0;
+    h.dycore.init_supercell(h.coupler, state, tracers);
+    copy_to(state, st); copy_to(tracers, tr);
+    return 0;
+  } catch (...) { return 1; }
 }
 
 } // extern "C"

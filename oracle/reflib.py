@@ -75,6 +75,12 @@ def load(ord=5, omp=False):
     lib.ref_gll9.restype = None
     lib.ref_init_supercell.argtypes = [C.c_void_p]
     lib.ref_init_thermal.argtypes = [C.c_void_p]
+    lib.ref_halo_exchange.argtypes = [C.c_void_p, _dp, _dp, _dp]
+    lib.ref_compute_tendencies_haloed.argtypes = [C.c_void_p, _dp, _dp, _dp, _dp, C.c_double]
+    lib.ref_convert_coupler_to_dynamics.argtypes = [C.c_void_p, _dp, _dp]
+    lib.ref_convert_dynamics_to_coupler.argtypes = [C.c_void_p, _dp, _dp]
+    lib.ref_compute_mass_dynamics.argtypes = [C.c_void_p, _dp, _dp, _dp]
+    lib.ref_init_supercell_dynamics.argtypes = [C.c_void_p, _dp, _dp]
     lib.ref_shutdown.restype = None
     atexit.register(lib.ref_shutdown)
     _libs[key] = lib
@@ -258,3 +264,32 @@ class RefDycore:
 
     def time_steps_raw(self, nsteps):
         return self.lib.ref_time_steps_raw(self.h, nsteps)
+
+    # ---- the reference's own public methods on caller-owned HALOED arrays (modified in place) ----
+    def halo_shape(self):
+        hs = self.hs
+        return (self.nz + 2 * hs, self.ny + 2 * hs, self.nx + 2 * hs, self.nens)
+
+    def halo_exchange(self, state, tracers, pressure):
+        assert self.lib.ref_halo_exchange(self.h, _p(state), _p(tracers), _p(pressure)) == 0
+
+    def compute_tendencies_haloed(self, state, tracers, tracers_tend, dt):
+        st = np.empty((5,) + self.shape4)
+        assert self.lib.ref_compute_tendencies_haloed(self.h, _p(state), _p(st), _p(tracers), _p(tracers_tend), float(dt)) == 0
+        return st
+
+    def convert_coupler_to_dynamics(self, state, tracers):
+        assert self.lib.ref_convert_coupler_to_dynamics(self.h, _p(state), _p(tracers)) == 0
+
+    def convert_dynamics_to_coupler(self, state, tracers):
+        assert self.lib.ref_convert_dynamics_to_coupler(self.h, _p(state), _p(tracers)) == 0
+
+    def compute_mass_dynamics(self, state, tracers):
+        out = np.empty((self.nt + 2, self.nens))
+        assert self.lib.ref_compute_mass_dynamics(self.h, _p(state), _p(tracers), _p(out)) == 0
+        return out
+
+    def init_supercell_dynamics(self):
+        st = np.empty((5,) + self.halo_shape()); tr = np.empty((max(self.nt, 1),) + self.halo_shape())
+        assert self.lib.ref_init_supercell_dynamics(self.h, _p(st), _p(tr)) == 0
+        return st, tr[:self.nt]

@@ -291,6 +291,10 @@ struct FieldPtrs {
   double *const *tr;   // device array of nt device pointers
 };
 
+}  // namespace awfl
+#include "awfl_haloed.cuh"
+namespace awfl {
+
 __device__ __forceinline__ double atomic_min_pos(double *addr, double v) {
   // positive doubles order like their bit patterns
   unsigned long long old = atomicMin((unsigned long long *)addr, (unsigned long long)__double_as_longlong(v));
@@ -533,7 +537,7 @@ __global__ void __launch_bounds__(128) k_init_thermal_column(const Geom g, const
 // spec 0: thermal, 1: supercell. One thread per cell; writes the coupler fields.
 __global__ void __launch_bounds__(128)
 k_init_cells(const Geom g, const Phys ph, const InitArgs a, const FieldPtrs fp, int idWV, const unsigned char *adds_mass, int spec,
-             const RowMap rm) {
+             const RowMap rm, double *dyn_st, double *dyn_tr, const HaloDims hdim) {
   long cell; int k, j, i, e;
   if (!row_coords(g, rm, cell, k, j, i, e)) return;
   const double z0 = a.zint[(long)k * g.nens + e], z1 = a.zint[(long)(k + 1) * g.nens + e];
@@ -575,6 +579,14 @@ k_init_cells(const Geom g, const Phys ph, const InitArgs a, const FieldPtrs fp, 
           rho += hd * wt;
           rt += hd * theta * wt;
         }
+  }
+  if (dyn_st) {
+    // Dycore::init_supercell (Dycore.h:1096-1276) proper: the haloed dynamics arrays, interior cells
+    const long hi = hidx(g, hdim, hdim.hs + k, hdim.hs + j, hdim.hs + i, e);
+    dyn_st[idR * hdim.nh + hi] = rho; dyn_st[idU * hdim.nh + hi] = ru; dyn_st[idV * hdim.nh + hi] = rv;
+    dyn_st[idW * hdim.nh + hi] = rw; dyn_st[idT * hdim.nh + hi] = rt;
+    for (int t = 0; t < g.nt; t++) dyn_tr[t * hdim.nh + hi] = t == idWV ? wv : 0.0;
+    return;
   }
   // convert_dynamics_to_coupler, Dycore.h:1313-1330
   const double theta = rt / rho;
@@ -640,6 +652,7 @@ struct awfl_handle {
   std::vector<cudaEvent_t> slab_ev;      // 2 events per slab: inputs on the device / results ready on the device
   double *tmp_state;     // scratch for awfl_compute_tendencies
   double *pcache;        // pressure of the current stage input (SweepArgs::pcache)
+  double *halo_pressure; // haloed pressure scratch of awfl_compute_tendencies_haloed (allocated on first use)
 };
 
 // Process-wide state is limited to these two objects. The message of a failed awfl_create is per host thread (one
@@ -1049,7 +1062,7 @@ int awfl_create(const awfl_config *cfg, awfl_handle **out) {
   ALLOC(h->positive_d, nt); ALLOC(h->adds_mass_d, nt);
   ALLOC(h->trptr_d, sizeof(double *) * nt);
   ALLOC(h->trptr_out_d, sizeof(double *) * nt);
-  h->stage_fields = nullptr; h->stage_out = nullptr; h->tmp_state = nullptr;
+  h->stage_fields = nullptr; h->stage_out = nullptr; h->tmp_state = nullptr; h->halo_pressure = nullptr;
   { const char *ev = getenv("AWFL_FUSED_FCT"); h->fused_fct = !(ev && atoi(ev) == 0); }
   h->s_in = nullptr; h->s_out = nullptr; h->host_last_ncycles = 0; h->host_mispredictions = 0;
   {
@@ -1086,7 +1099,7 @@ void awfl_destroy(awfl_handle *h) {
   release_cvtab(h);
   cudaFree(h->mult); cudaFree(h->dz); cudaFree(h->rdz); cudaFree(h->grav_var); cudaFree(h->vtab); cudaFree(h->vs2c); cudaFree(h->vwrl);
   cudaFree(h->pint); cudaFree(h->dt_min_d); cudaFree(h->mass_d); cudaFree(h->positive_d); cudaFree(h->adds_mass_d);
-  cudaFree(h->pcache); cudaFree(h->trptr_d); cudaFree(h->trptr_out_d); cudaFree(h->stage_fields); cudaFree(h->stage_out); cudaFree(h->tmp_state);
+  cudaFree(h->pcache); cudaFree(h->halo_pressure); cudaFree(h->trptr_d); cudaFree(h->trptr_out_d); cudaFree(h->stage_fields); cudaFree(h->stage_out); cudaFree(h->tmp_state);
   if (h->s_in) { cudaStreamDestroy(h->s_in); cudaStreamDestroy(h->s_out); for (int c = 0; c < 4; c++) cudaStreamDestroy(h->s_cmp[c]); }
   for (cudaEvent_t e : h->slab_ev) cudaEventDestroy(e);
   if (h->dt_min_h) cudaFreeHost(h->dt_min_h);
@@ -1451,13 +1464,12 @@ int awfl_declare_hydrostatic(awfl_handle *h, const awfl_fields *f, const awfl_gc
   return 0;
 }
 
-int awfl_init_idealized(awfl_handle *h, const awfl_fields *f, const double *zint, int data_spec) {
-  ENTER(h);
-  if (data_spec != 0 && data_spec != 1) return fail(h, "awfl_init_idealized: data_spec must be 0 (thermal) or 1 (supercell)");
-  if (!zint) return fail(h, "awfl_init_idealized: vertical_interface_height is required");
+// Idealized initial state into the coupler fields (dyn_st == NULL) or into haloed dynamics arrays.
+static int init_idealized(awfl_handle *h, const awfl_fields *f, const double *zint, int data_spec, double *dyn_st, double *dyn_tr) {
   const Geom &g = h->g;
   FieldPtrs fp;
-  if (make_field_ptrs(h, f, fp)) return 1;
+  memset(&fp, 0, sizeof(fp));
+  if (f && make_field_ptrs(h, f, fp)) return 1;
   // init-time scratch (not a time-step path): pressure / vapour at the 9 GLL points of every cell + two columns
   const size_t n2 = (size_t)g.nz * g.nens;
   double *scratch = nullptr;
@@ -1468,11 +1480,101 @@ int awfl_init_idealized(awfl_handle *h, const awfl_fields *f, const double *zint
   if (data_spec == 1) k_init_supercell_column<<<(unsigned)(g.nens + 63) / 64, 64, 0, h->stream>>>(g, h->ph, a);
   else k_init_thermal_column<<<dim3((unsigned)(g.nens + 127) / 128, (unsigned)g.nz), 128, 0, h->stream>>>(g, h->ph, a);
   const RowMap rm = row_map(g, 128);
-  k_init_cells<<<row_blocks(g, rm), 128, 0, h->stream>>>(g, h->ph, a, fp, h->cfg.idWV, h->adds_mass_d, data_spec, rm);
+  k_init_cells<<<row_blocks(g, rm), 128, 0, h->stream>>>(g, h->ph, a, fp, h->cfg.idWV, h->adds_mass_d, data_spec, rm, dyn_st, dyn_tr,
+                                                         halo_dims(g, h->hs));
   h->launches += 2;
   cudaError_t e1 = cudaGetLastError(), e2 = cudaStreamSynchronize(h->stream);
   cudaFree(scratch);
   if (e1 != cudaSuccess || e2 != cudaSuccess) return fail(h, std::string("awfl_init_idealized: ") + cudaGetErrorString(e1 != cudaSuccess ? e1 : e2));
+  return 0;
+}
+
+int awfl_init_idealized(awfl_handle *h, const awfl_fields *f, const double *zint, int data_spec) {
+  ENTER(h);
+  if (data_spec != 0 && data_spec != 1) return fail(h, "awfl_init_idealized: data_spec must be 0 (thermal) or 1 (supercell)");
+  if (!zint) return fail(h, "awfl_init_idealized: vertical_interface_height is required");
+  return init_idealized(h, f, zint, data_spec, nullptr, nullptr);
+}
+
+int awfl_init_supercell(awfl_handle *h, double *state, double *tracers, const double *zint) {
+  ENTER(h);
+  if (!state || !tracers || !zint) return fail(h, "awfl_init_supercell: NULL pointer");
+  return init_idealized(h, nullptr, zint, 1, state, tracers);
+}
+
+// ---- the reference's haloed dynamics arrays at the boundary (awfl_haloed.cuh) ----
+int awfl_convert_coupler_to_dynamics(awfl_handle *h, const awfl_fields *f, double *state, double *tracers) {
+  ENTER(h);
+  FieldPtrs fp;
+  if (make_field_ptrs(h, f, fp)) return 1;
+  const RowMap rm = row_map(h->g, 256);
+  k_h_convert_in<<<row_blocks(h->g, rm), 256, 0, h->stream>>>(h->g, h->ph, fp, h->cfg.idWV, h->adds_mass_d, rm, halo_dims(h->g, h->hs), state, tracers);
+  h->launches++;
+  CK(cudaGetLastError());
+  return 0;
+}
+
+int awfl_convert_dynamics_to_coupler(awfl_handle *h, const double *state, const double *tracers, const awfl_fields *f) {
+  ENTER(h);
+  FieldPtrs fp;
+  if (make_field_ptrs(h, f, fp)) return 1;
+  const RowMap rm = row_map(h->g, 256);
+  k_h_convert_out<<<row_blocks(h->g, rm), 256, 0, h->stream>>>(h->g, h->ph, fp, h->cfg.idWV, h->adds_mass_d, rm, halo_dims(h->g, h->hs), state, tracers);
+  h->launches++;
+  CK(cudaGetLastError());
+  return 0;
+}
+
+static void launch_halo_exchange(awfl_handle *h, double *state, double *tracers, double *pressure) {
+  const Geom &g = h->g;
+  const HaloDims d = halo_dims(g, h->hs);
+  const unsigned nv = (unsigned)(NS + g.nt + 1);
+  const long nx_ = (long)g.nz * g.ny * d.hs * g.nens, ny_ = (long)g.nz * d.hs * g.nx * g.nens, nw = (long)g.ny * g.nx * g.nens;
+  k_h_periodic<<<dim3((unsigned)((nx_ + 255) / 256), nv), 256, 0, h->stream>>>(g, d, 0, state, tracers, pressure);
+  if (!g.sim2d) k_h_periodic<<<dim3((unsigned)((ny_ + 255) / 256), nv), 256, 0, h->stream>>>(g, d, 1, state, tracers, pressure);
+  k_h_wall<<<(unsigned)((nw + 127) / 128), 128, 0, h->stream>>>(g, h->ph, d, h->dz, state, tracers, pressure);
+  h->launches += g.sim2d ? 2 : 3;
+}
+
+int awfl_halo_exchange(awfl_handle *h, double *state, double *tracers, double *pressure) {
+  ENTER(h);
+  if (!state || !tracers || !pressure) return fail(h, "awfl_halo_exchange: NULL pointer");
+  launch_halo_exchange(h, state, tracers, pressure);
+  CK(cudaGetLastError());
+  return 0;
+}
+
+int awfl_compute_tendencies_haloed(awfl_handle *h, double *state, double *state_tend, double *tracers, double *tracers_tend, double dt) {
+  ENTER(h);
+  const Geom &g = h->g;
+  const HaloDims d = halo_dims(g, h->hs);
+  const RowMap rm = row_map(g, 256);
+  const unsigned blocks = row_blocks(g, rm);
+  // the right-hand side itself: the marching kernels on the gathered interior; the FCT start mass is what the caller left in
+  // tracers_tend (Dycore.h:158,173,197 -> :536)
+  k_h_gather<<<blocks, 256, 0, h->stream>>>(g, rm, d, state, tracers, h->Q[1]);
+  h->launches++;
+  run_stage(h, g, h->Q[1], h->Q[1], nullptr, 0.0, 1.0, dt, dt, 1.0, 0.0, 2, tracers_tend, state_tend, tracers_tend);
+  // what the reference leaves in the caller's arrays (the SSPRK3 update of timeStep consumes it, Dycore.h:164,184,208):
+  // interior divided by density and multiplied back, ghosts filled from the divided values
+  if (!h->halo_pressure) CK(cudaMalloc((void **)&h->halo_pressure, sizeof(double) * (size_t)d.nh));
+  k_h_divide_multiply<<<blocks, 256, 0, h->stream>>>(g, h->ph, rm, d, state, tracers, h->halo_pressure, 0);
+  launch_halo_exchange(h, state, tracers, h->halo_pressure);
+  k_h_divide_multiply<<<blocks, 256, 0, h->stream>>>(g, h->ph, rm, d, state, tracers, h->halo_pressure, 1);
+  h->launches += 2;
+  CK(cudaGetLastError());
+  return 0;
+}
+
+int awfl_compute_mass_dynamics(awfl_handle *h, const double *state, const double *tracers, double *out_device) {
+  ENTER(h);
+  const Geom &g = h->g;
+  const RowMap rm = row_map(g, 256);
+  k_h_gather<<<row_blocks(g, rm), 256, 0, h->stream>>>(g, rm, halo_dims(g, h->hs), state, tracers, h->Q[1]);
+  const long n = (long)(g.nt + 2) * g.nens;
+  k_mass<<<(unsigned)((n + 127) / 128), 128, 0, h->stream>>>(g, h->Q[1], h->dz, out_device);
+  h->launches += 2;
+  CK(cudaGetLastError());
   return 0;
 }
 

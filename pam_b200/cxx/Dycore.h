@@ -13,11 +13,13 @@
 // get_data_manager_device_readwrite/readonly with get<T,N>(name) -> array with .data(), register_and_allocate<T>,
 // entry_exists.
 #pragma once
+#include <cmath>
 #include <cstdio>
 #include <string>
 #include <vector>
 
 #include "../../include/awfl_b200.h"
+#include "../csrc/awfl_tables.h"
 
 #ifndef PAM_B200_REAL_DEFINED
 #define PAM_B200_REAL_DEFINED
@@ -30,6 +32,61 @@ namespace awfl_b200_detail {
   std::fprintf(stderr, "%s\n", msg.c_str());
   throw std::string(msg);
 }
+
+// Dycore::reconstruct is YAKL_INLINE in the reference (callable from host and device code alike, Dycore.h:591)
+#if defined(YAKL_INLINE)
+#define AWFL_B200_INLINE YAKL_INLINE
+#elif defined(__CUDACC__)
+#define AWFL_B200_INLINE __host__ __device__ inline
+#else
+#define AWFL_B200_INLINE inline
+#endif
+
+// TransformMatrices::coefs_to_tv (TransformMatrices.h:188,871,2263,4734): the truncated total variation of a polynomial as
+// a sparse quadratic form in its coefficients (tables generated from exact rationals by tools/gen_tables.py)
+template <int N> struct TvForm;
+#define AWFL_B200_TVFORM(O)                                                                                          \
+  template <> struct TvForm<(O + 1) / 2> {                                                                           \
+    template <class A> AWFL_B200_INLINE static double eval(A const &a) {                                             \
+      const int I[] = AWFL_TVLO_I_##O##_INIT, J[] = AWFL_TVLO_J_##O##_INIT;                                          \
+      const double C[] = AWFL_TVLO_C_##O##_INIT;                                                                     \
+      double r = 0.;                                                                                                 \
+      for (int t = 0; t < AWFL_TVLO_N_##O; t++) r += I[t] == J[t] ? C[t] * (a[I[t]] * a[I[t]]) : C[t] * a[I[t]] * a[J[t]]; \
+      return r;                                                                                                      \
+    }                                                                                                                \
+  };                                                                                                                 \
+  template <> struct TvForm<O> {                                                                                     \
+    template <class A> AWFL_B200_INLINE static double eval(A const &a) {                                             \
+      const int I[] = AWFL_TVHI_I_##O##_INIT, J[] = AWFL_TVHI_J_##O##_INIT;                                          \
+      const double C[] = AWFL_TVHI_C_##O##_INIT;                                                                     \
+      double r = 0.;                                                                                                 \
+      for (int t = 0; t < AWFL_TVHI_N_##O; t++) r += I[t] == J[t] ? C[t] * (a[I[t]] * a[I[t]]) : C[t] * a[I[t]] * a[J[t]]; \
+      return r;                                                                                                      \
+    }                                                                                                                \
+  };
+#ifdef MW_ORD
+#if MW_ORD == 3
+AWFL_B200_TVFORM(3)
+#elif MW_ORD == 7
+AWFL_B200_TVFORM(7)
+#elif MW_ORD == 9
+AWFL_B200_TVFORM(9)
+#else
+AWFL_B200_TVFORM(5)
+#endif
+#else
+AWFL_B200_TVFORM(5)
+#endif
+
+// the (num_tracers+2, nens) device array Dycore::compute_mass returns, by the type of the dynamics arrays passed in:
+// the reference's real2d inside a PAM build (YAKL), the coupler look-alike's own array type otherwise
+template <class A5> struct MassArray;
+#ifdef YAKL_INLINE
+template <class T> struct MassArray<yakl::Array<T, 5, yakl::memDevice, yakl::styleC>> {
+  typedef yakl::Array<double, 2, yakl::memDevice, yakl::styleC> type;
+  static type make(int nv, int nens) { return type("mass", nv, nens); }
+};
+#endif
 }  // namespace awfl_b200_detail
 
 class Dycore {
@@ -130,7 +187,21 @@ class Dycore {
     Fields<Coupler> f(coupler, nt_);
     auto &dm = coupler.get_data_manager_device_readwrite();
     check(awfl_set_variable_gravity(h_, dm.template get<real const, 2>("variable_gravity").data()), "awfl_set_variable_gravity");
+#ifdef PAM_DEBUG
+    const std::vector<real> mass_init = compute_mass(coupler);                               // Dycore.h:136-138
+#endif
     check(awfl_time_step(h_, &f.f, coupler.template get_option<real>("crm_dt"), 0, nullptr), "awfl_time_step");
+#ifdef PAM_DEBUG
+    // Dycore.h:224-251: warn where a (variable, member) mass changed by more than 1e-10 both relatively and absolutely
+    const std::vector<real> mass_final = compute_mass(coupler);
+    const int nens = coupler.get_nens();
+    for (size_t q = 0; q < mass_init.size(); q++) {
+      const double diff = mass_final[q] - mass_init[q], rel = std::fabs(diff) / (std::fabs(mass_init[q]) + 1.e-20);
+      if (rel > 1.e-10 && std::fabs(diff) > 1.e-10)
+        std::printf("WARNING: conservation violated variable,ensemble,rel_diff,mass_diff,init,final: %d , %d , %10.6e , %10.6e , %10.6e , %10.6e\n",
+                    (int)(q / nens), (int)(q % nens), rel, diff, mass_init[q], mass_final[q]);
+    }
+#endif
   }
 
   // Dycore::compute_time_step (Dycore.h:65-102)
@@ -166,6 +237,101 @@ class Dycore {
     std::vector<real> out((size_t)(nt_ + 2) * coupler.get_nens());
     check(awfl_compute_mass(h_, &f.f, out.data()), "awfl_compute_mass");
     return out;
+  }
+
+  // ---- the reference's methods on its HALOED dynamics arrays: real5d (5 | num_tracers, nz+2hs, ny+2hs, nx+2hs, nens) ----
+  // Any array type with .data() works: yakl::Array inside a PAM build, the look-alike's views elsewhere.
+
+  // Dycore::compute_mass (Dycore.h:37-60): (num_tracers+2, nens) device array of per-member means of q*dz
+  template <class Coupler, class A5>
+  typename awfl_b200_detail::MassArray<A5>::type compute_mass(Coupler const &coupler, A5 const &state, A5 const &tracers) const {
+    typedef awfl_b200_detail::MassArray<A5> M;
+    typename M::type mass = M::make(nt_ + 2, coupler.get_nens());
+    check(awfl_compute_mass_dynamics(h_, state.data(), tracers.data(), mass.data()), "awfl_compute_mass_dynamics");
+    return mass;
+  }
+
+  // Dycore::compute_tendencies (Dycore.h:262-586): tracers_tend carries the FCT start mass in and the tendencies out;
+  // state / tracers come back divided by density and multiplied back, ghosts filled (what the SSPRK3 update consumes)
+  template <class Coupler, class A5>
+  void compute_tendencies(Coupler &coupler, A5 const &state, A5 const &state_tend, A5 const &tracers, A5 const &tracers_tend, real dt) const {
+    auto &dm = coupler.get_data_manager_device_readwrite();
+    check(awfl_set_variable_gravity(h_, dm.template get<real const, 2>("variable_gravity").data()), "awfl_set_variable_gravity");   // Dycore.h:277
+    check(awfl_compute_tendencies_haloed(h_, state.data(), state_tend.data(), tracers.data(), tracers_tend.data(), dt),
+          "awfl_compute_tendencies_haloed");
+  }
+
+  // Dycore::reconstruct (Dycore.h:591-604) + weno::compute_weno_coefs (WenoLimiter.h:98-181) with caller-supplied matrices:
+  // value of the WENO-limited polynomial of the centre cell at its left (ind = 0) or right (ind = 1) edge. Host- and
+  // device-callable like the reference's; the time step itself uses the fused row form of csrc/awfl_weno.cuh instead.
+  template <class S1, class C2G, class S2C, class WRL, class IDL>
+  AWFL_B200_INLINE static real reconstruct(S1 const &stencil, C2G const &coefs_to_gll, S2C const &sten_to_coefs, WRL const &weno_recon_lower,
+                                           IDL const &idl, real sigma, int ind) {
+    const real eps = 1.0e-20;
+    real a_lo[hs][hs], a_hi[ord], tv[hs + 1], wts[hs + 1];
+    for (int i = 0; i < hs; i++)
+      for (int ii = 0; ii < hs; ii++) {
+        real tmp = 0;
+        for (int s = 0; s < hs; s++) tmp += weno_recon_lower(i, s, ii) * stencil(i + s);
+        a_lo[i][ii] = tmp;
+      }
+    for (int ii = 0; ii < ord; ii++) {
+      real tmp = 0;
+      for (int s = 0; s < ord; s++) tmp += sten_to_coefs(s, ii) * stencil(s);
+      a_hi[ii] = tmp;
+    }
+    for (int i = 0; i < hs; i++)                                   // the "bridge" polynomial, WenoLimiter.h:131-138
+      for (int ii = 0; ii < hs; ii++) a_hi[ii] -= idl(i) * a_lo[i][ii];
+    for (int ii = 0; ii < ord; ii++) a_hi[ii] /= idl(hs);
+    real lo_avg = 0;
+    for (int i = 0; i < hs; i++) { tv[i] = awfl_b200_detail::TvForm<hs>::eval(a_lo[i]); lo_avg += tv[i]; }
+    lo_avg /= hs;
+    tv[hs] = lo_avg + (awfl_b200_detail::TvForm<ord>::eval(a_hi) - lo_avg) * sigma;
+    real sum = 0;
+    for (int i = 0; i < hs + 1; i++) { wts[i] = idl(i) / (tv[i] * tv[i] + eps); sum += wts[i]; }
+    for (int i = 0; i < hs + 1; i++) wts[i] /= (sum + eps);        // convexify, WenoLimiter.h:23-29
+    sum = 0;
+    for (int i = 0; i < hs + 1; i++) {                             // map_weights, WenoLimiter.h:11-19
+      const real d = idl(i), w = wts[i];
+      wts[i] = w * (d + d * d - 3 * d * w + w * w) / (d * d + w * (1 - 2 * d));
+      sum += wts[i];
+    }
+    for (int i = 0; i < hs + 1; i++) wts[i] /= (sum + eps);
+    real val = 0;
+    for (int s = 0; s < ord; s++) {
+      real aw = wts[hs] * a_hi[s];
+      if (s < hs) for (int i = 0; i < hs; i++) aw += wts[i] * a_lo[i][s];
+      val += coefs_to_gll(s, ind) * aw;
+    }
+    return val;
+  }
+
+  // Dycore::halo_exchange (Dycore.h:608-711): periodic x / y ghosts, wall ghosts in z, on the divided arrays
+  template <class Coupler, class A5, class A4>
+  void halo_exchange(Coupler const & /*coupler*/, A5 const &state, A5 const &tracers, A4 const &pressure) const {
+    check(awfl_halo_exchange(h_, state.data(), tracers.data(), pressure.data()), "awfl_halo_exchange");
+  }
+
+  // Dycore::init_supercell (Dycore.h:1096-1276): interior of state / tracers
+  template <class Coupler, class A5>
+  void init_supercell(Coupler &coupler, A5 &state, A5 &tracers) {
+    auto &dm = coupler.get_data_manager_device_readwrite();
+    check(awfl_init_supercell(h_, state.data(), tracers.data(), dm.template get<real const, 2>("vertical_interface_height").data()),
+          "awfl_init_supercell");
+  }
+
+  // Dycore::convert_dynamics_to_coupler (Dycore.h:1281-1331)
+  template <class Coupler, class A5>
+  void convert_dynamics_to_coupler(Coupler &coupler, A5 const &state, A5 const &tracers) const {
+    Fields<Coupler> f(coupler, nt_);
+    check(awfl_convert_dynamics_to_coupler(h_, state.data(), tracers.data(), &f.f), "awfl_convert_dynamics_to_coupler");
+  }
+
+  // Dycore::convert_coupler_to_dynamics (Dycore.h:1336-1388)
+  template <class Coupler, class A5>
+  void convert_coupler_to_dynamics(Coupler &coupler, A5 &state, A5 &tracers) const {
+    Fields<Coupler> f(coupler, nt_);
+    check(awfl_convert_coupler_to_dynamics(h_, &f.f, state.data(), tracers.data()), "awfl_convert_coupler_to_dynamics");
   }
 
   // Dycore::finalize (Dycore.h:1548)
@@ -224,7 +390,7 @@ class Dycore {
   static void set_default(Coupler &c, const char *key, T v) {
     if (!c.option_exists(key)) c.template set_option<T>(key, v);
   }
-  void check(int rc, const char *what) {
+  void check(int rc, const char *what) const {
     if (rc != 0) awfl_b200_detail::endrun(std::string(what) + ": " + awfl_last_error(h_));
   }
   void release() {

@@ -29,6 +29,38 @@ struct ArrayView {
   long totElems() const { long n = 1; for (int i = 0; i < N; i++) n *= dims[i]; return n; }
 };
 
+// Owning device array created by a caller (the look-alike of `real5d state("state",5,nz+2*hs,...)`): zero-filled
+// device memory from the C ABI's runtime helpers, freed with the last copy's owner. Move-only.
+template <class T, int N>
+class DeviceArray {
+ public:
+  DeviceArray() : ptr_(nullptr) { for (int i = 0; i < N; i++) dims_[i] = 0; }
+  DeviceArray(std::initializer_list<int> dims) : ptr_(nullptr) {
+    int i = 0;
+    for (int d : dims) if (i < N) dims_[i++] = d;
+    void *p = nullptr;
+    if (awfl_device_alloc(&p, (unsigned long)totElems() * sizeof(T)) != 0) endrun("ERROR: device allocation failed");
+    ptr_ = (T *)p;
+  }
+  DeviceArray(DeviceArray &&o) noexcept : ptr_(o.ptr_) { for (int i = 0; i < N; i++) dims_[i] = o.dims_[i]; o.ptr_ = nullptr; }
+  DeviceArray &operator=(DeviceArray &&o) noexcept {
+    if (this != &o) { awfl_device_free(ptr_); ptr_ = o.ptr_; for (int i = 0; i < N; i++) dims_[i] = o.dims_[i]; o.ptr_ = nullptr; }
+    return *this;
+  }
+  DeviceArray(const DeviceArray &) = delete;
+  DeviceArray &operator=(const DeviceArray &) = delete;
+  ~DeviceArray() { awfl_device_free(ptr_); }
+  T *data() const { return ptr_; }
+  int extent(int i) const { return dims_[i]; }
+  long totElems() const { long n = 1; for (int i = 0; i < N; i++) n *= dims_[i]; return n; }
+  void read(T *host) const { if (awfl_copy_to_host(host, ptr_, (unsigned long)totElems() * sizeof(T))) endrun("ERROR: copy to host failed"); }
+  void write(const T *host) { if (awfl_copy_to_device(ptr_, host, (unsigned long)totElems() * sizeof(T))) endrun("ERROR: copy to device failed"); }
+
+ private:
+  T *ptr_;
+  int dims_[N];
+};
+
 class DataManager {
  public:
   DataManager() {}
@@ -219,3 +251,12 @@ class PamCoupler {
 };
 
 }  // namespace pam_b200
+
+// Dycore::compute_mass(coupler, state, tracers) returns an owning (num_tracers+2, nens) device array of this header's kind
+namespace awfl_b200_detail {
+template <class T> struct MassArray<pam_b200::DeviceArray<T, 5>> {
+  typedef pam_b200::DeviceArray<double, 2> type;
+  static type make(int nv, int nens) { return type({nv, nens}); }
+};
+template <class T> struct MassArray<pam_b200::ArrayView<T, 5>> : MassArray<pam_b200::DeviceArray<double, 5>> {};
+}  // namespace awfl_b200_detail

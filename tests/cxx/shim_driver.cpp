@@ -3,6 +3,10 @@
 // set_grid, add tracers, dycore.init, then coupler.run_module("dycore", [&](auto &c){ dycore.timeStep(c); }).
 //   shim_driver selftest            no GPU needed: names, DataManager/Options errors, init must fail loudly without a GPU
 //   shim_driver run IN OUT NSTEPS   reads a case written by tests/test_cxx_shim.py, steps it, writes the fields back
+//   shim_driver dynamics IN OUT     the reference's other public methods on caller-owned HALOED arrays (Dycore.h:37,262,608,
+//                                   1096,1281,1336): convert in, compute_mass, compute_tendencies, halo_exchange, convert out,
+//                                   init_supercell -- every array is dumped for the Python test to compare with the oracle
+//   shim_driver reconstruct IN OUT  no GPU needed: the static Dycore::reconstruct (Dycore.h:591-604) on stencils from IN
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -116,11 +120,140 @@ static int run(const char *in, const char *out, int nsteps, bool mmf) {
   return 0;
 }
 
+// small fixed-size matrices with the SArray call syntax, filled from the uniform-grid tables of the order compiled in
+template <int D0, int D1 = 1, int D2 = 1> struct Mat {
+  double v[D0 * D1 * D2];
+  double operator()(int i) const { return v[i]; }
+  double operator()(int i, int j) const { return v[i * D1 + j]; }
+  double operator()(int i, int j, int k) const { return v[(i * D1 + j) * D2 + k]; }
+};
+#define CAT3_(a, b, c) a##b##c
+#define CAT3(a, b, c) CAT3_(a, b, c)
+#ifndef MW_ORD
+#define MW_ORD_ 5
+#else
+#define MW_ORD_ MW_ORD
+#endif
+
+static int reconstruct_mode(const char *in, const char *out) {
+  constexpr int ord = Dycore::ord, hs = Dycore::hs;
+  Mat<ord, ord> s2c; Mat<ord, 2> c2g; Mat<hs, hs, hs> wrl; Mat<hs + 1> idl;
+  std::memcpy(s2c.v, CAT3(AWFL_S2C_, MW_ORD_, ), sizeof(s2c.v));
+  std::memcpy(c2g.v, CAT3(AWFL_C2G_, MW_ORD_, ), sizeof(c2g.v));
+  std::memcpy(wrl.v, CAT3(AWFL_WRL_, MW_ORD_, ), sizeof(wrl.v));
+  double sum = 0;                                                              // wenoSetIdealSigma, WenoLimiter.h:32-95
+  for (int i = 0; i < hs + 1; i++) sum += CAT3(AWFL_IDL_RAW_, MW_ORD_, )[i];
+  for (int i = 0; i < hs + 1; i++) idl.v[i] = CAT3(AWFL_IDL_RAW_, MW_ORD_, )[i] / (sum + 1.0e-20);
+  const double sigma = CAT3(AWFL_SIGMA_, MW_ORD_, );
+  FILE *f = std::fopen(in, "rb");
+  if (!f) return 2;
+  int n = 0;
+  rd(f, &n, sizeof(int));
+  std::vector<double> st((size_t)n * ord), res((size_t)2 * n);
+  rd(f, st.data(), sizeof(double) * st.size());
+  std::fclose(f);
+  for (int q = 0; q < n; q++) {
+    Mat<ord> u;
+    for (int s = 0; s < ord; s++) u.v[s] = st[(size_t)q * ord + s];
+    for (int ind = 0; ind < 2; ind++) res[(size_t)ind * n + q] = Dycore::reconstruct(u, c2g, s2c, wrl, idl, sigma, ind);
+  }
+  FILE *g = std::fopen(out, "wb");
+  std::fwrite(res.data(), sizeof(double), res.size(), g);
+  std::fclose(g);
+  return 0;
+}
+
+static int dynamics_mode(const char *in, const char *out) {
+  using pam_b200::DeviceArray;
+  FILE *f = std::fopen(in, "rb");
+  if (!f) { std::printf("cannot open %s\n", in); return 2; }
+  int hdr[6];
+  rd(f, hdr, sizeof(hdr));
+  const int nz = hdr[0], ny = hdr[1], nx = hdr[2], nens = hdr[3], nt = hdr[4];
+  double par[9];
+  rd(f, par, sizeof(par));
+  std::vector<double> zint(nz + 1);
+  rd(f, zint.data(), sizeof(double) * (nz + 1));
+  std::vector<std::string> tnames(nt);
+  std::vector<int> tpos(nt), tadds(nt);
+  for (int t = 0; t < nt; t++) {
+    char name[32]; int flags[2];
+    rd(f, name, 32); rd(f, flags, sizeof(flags));
+    tnames[t] = name; tpos[t] = flags[0]; tadds[t] = flags[1];
+  }
+  PamCoupler coupler;
+  coupler.set_option<real>("crm_dt", par[2]);
+  coupler.set_option<real>("R_d", par[3]); coupler.set_option<real>("cp_d", par[4]); coupler.set_option<real>("R_v", par[5]);
+  coupler.set_option<real>("cp_v", par[6]); coupler.set_option<real>("p0", par[7]); coupler.set_option<real>("grav", par[8]);
+  coupler.allocate_coupler_state(nz, ny, nx, nens);
+  coupler.set_grid(par[0], par[1], zint);
+  for (int t = 0; t < nt; t++) coupler.add_tracer(tnames[t], tnames[t], tpos[t] != 0, tadds[t] != 0);
+  Dycore dycore;
+  dycore.init(coupler);
+  std::vector<std::string> names = {"density_dry", "uvel", "vvel", "wvel", "temp"};
+  for (auto &n : tnames) names.push_back(n);
+  const size_t ncell = (size_t)nz * ny * nx * nens;
+  std::vector<double> buf(ncell), fct((size_t)nt * ncell);
+  auto &dm = coupler.get_data_manager_device_readwrite();
+  for (size_t v = 0; v < names.size(); v++) {
+    rd(f, buf.data(), sizeof(double) * ncell);
+    dm.write<real>(names[v], buf.data());
+    if (v >= 5) for (size_t q = 0; q < ncell; q++) fct[(v - 5) * ncell + q] = buf[q] > 0 ? buf[q] : 0.;
+  }
+  std::fclose(f);
+  dycore.declare_current_profile_as_hydrostatic(coupler);
+  const int hs = Dycore::hs;
+  // what Dycore::timeStep declares (Dycore.h:122-126,149-152), zero-filled
+  DeviceArray<real, 5> state({Dycore::num_state, nz + 2 * hs, ny + 2 * hs, nx + 2 * hs, nens}), tracers({nt, nz + 2 * hs, ny + 2 * hs, nx + 2 * hs, nens});
+  DeviceArray<real, 5> state_tend({Dycore::num_state, nz, ny, nx, nens}), tracers_tend({nt, nz, ny, nx, nens});
+  DeviceArray<real, 4> pressure({nz + 2 * hs, ny + 2 * hs, nx + 2 * hs, nens});
+  FILE *g = std::fopen(out, "wb");
+  auto dump = [&](auto const &a) {
+    std::vector<double> h((size_t)a.totElems());
+    a.read(h.data());
+    std::fwrite(h.data(), sizeof(double), h.size(), g);
+  };
+  dycore.convert_coupler_to_dynamics(coupler, state, tracers);
+  dump(state); dump(tracers);
+  auto mass = dycore.compute_mass(coupler, state, tracers);
+  dump(mass);
+  tracers_tend.write(fct.data());
+  dycore.compute_tendencies(coupler, state, state_tend, tracers, tracers_tend, 0.7);
+  dump(state); dump(tracers); dump(state_tend); dump(tracers_tend);
+  dycore.convert_dynamics_to_coupler(coupler, state, tracers);
+  for (auto &n : names) { dm.read<real>(n, buf.data()); std::fwrite(buf.data(), sizeof(double), ncell, g); }
+  // halo_exchange on its own: divide the interior first, as compute_tendencies does (the test repeats this in numpy)
+  {
+    std::vector<double> hst((size_t)state.totElems()), htr((size_t)tracers.totElems());
+    state.read(hst.data()); tracers.read(htr.data());
+    const size_t nh = hst.size() / 5;
+    for (size_t q = 0; q < nh; q++) {
+      const double rho = hst[q];
+      if (rho == 0.) continue;
+      for (int l = 1; l < 5; l++) hst[l * nh + q] /= rho;
+      for (int t = 0; t < nt; t++) htr[t * nh + q] /= rho;
+    }
+    state.write(hst.data()); tracers.write(htr.data());
+  }
+  dycore.halo_exchange(coupler, state, tracers, pressure);
+  dump(state); dump(tracers); dump(pressure);
+  dycore.init_supercell(coupler, state, tracers);
+  dycore.convert_dynamics_to_coupler(coupler, state, tracers);
+  for (auto &n : names) { dm.read<real>(n, buf.data()); std::fwrite(buf.data(), sizeof(double), ncell, g); }
+  std::fclose(g);
+  dycore.finalize(coupler);
+  coupler.finalize();
+  std::printf("shim_driver: dynamics-array methods done\n");
+  return 0;
+}
+
 int main(int argc, char **argv) {
   try {
     if (argc >= 2 && !std::strcmp(argv[1], "selftest")) return selftest();
+    if (argc >= 4 && !std::strcmp(argv[1], "reconstruct")) return reconstruct_mode(argv[2], argv[3]);
+    if (argc >= 4 && !std::strcmp(argv[1], "dynamics")) return dynamics_mode(argv[2], argv[3]);
     if (argc >= 5 && !std::strcmp(argv[1], "run")) return run(argv[2], argv[3], std::atoi(argv[4]), argc >= 6 && !std::strcmp(argv[5], "mmf"));
   } catch (std::string &s) { std::printf("endrun: %s\n", s.c_str()); return 3; }
-  std::printf("usage: shim_driver selftest | run IN OUT NSTEPS [mmf]\n");
+  std::printf("usage: shim_driver selftest | run IN OUT NSTEPS [mmf] | dynamics IN OUT | reconstruct IN OUT\n");
   return 64;
 }

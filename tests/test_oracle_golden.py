@@ -120,3 +120,49 @@ def test_golden_vectors_reproduce_from_reference():
     for k, v in r.get_fields().items():
         assert rel_l2(v, z["s1_" + k], 1e-300) <= TOL, k
     r.close()
+
+
+@pytest.mark.skipif(not reflib.available(5), reason="oracle/_ref (compiled reference) not built on this host")
+@pytest.mark.parametrize("name", ["c2d_ord5", "c3d_ord5", "c2d_ord5_nt10", "c2d_ord3"])
+def test_oracle_haloed_methods_are_bit_identical_to_the_reference_methods(name):
+    """The reference's other public Dycore methods take its HALOED arrays (Dycore.h:37, :262, :608, :1281, :1336). The
+    oracle's restatements of them -- the checkers of the C ABI's awfl_*_haloed / awfl_convert_* / awfl_halo_exchange --
+    against the compiled reference's own methods on the same arrays, ghosts included."""
+    kw, ord, crm_dt = MG.CASES[name]
+    if not reflib.available(ord):
+        pytest.skip("reference library of this order not built")
+    case = MG.build_case(kw)
+    o = H.make_oracle(case, ord, crm_dt=crm_dt)
+    r = reflib.RefDycore(case["nz"], case["ny"], case["nx"], case["nens"], case["xlen"], case["ylen"], case["zint"],
+                         tracers=case["tracers"], consts=case["consts"], crm_dt=crm_dt, ord=ord)
+    r.set_fields(case["fields"])
+    o.declare_hydrostatic(); r.declare_hydrostatic()
+    nt, hsh, hs = len(case["tracers"]), o.halo_shape(), o.hs
+    assert hsh == r.halo_shape()
+    rng = np.random.default_rng(3)
+    junk = lambda n: rng.standard_normal((n,) + hsh)      # ghosts start as junk: every one the method owns is overwritten
+    so, to = junk(5), junk(nt)
+    sr, tr = so.copy(), to.copy()
+    o.convert_coupler_to_dynamics(so, to); r.convert_coupler_to_dynamics(sr, tr)
+    assert np.array_equal(so, sr) and np.array_equal(to, tr)
+    assert np.array_equal(o.compute_mass_dynamics(so, to), r.compute_mass_dynamics(sr, tr))
+    tto = np.ascontiguousarray(np.maximum(np.stack([case["fields"][t[0]] for t in case["tracers"]]), 0.0))
+    ttr = tto.copy()
+    sto = o.compute_tendencies_haloed(so, to, tto, 0.7)
+    str_ = r.compute_tendencies_haloed(sr, tr, ttr, 0.7)
+    assert np.array_equal(sto, str_) and np.array_equal(tto, ttr)
+    assert np.array_equal(so, sr) and np.array_equal(to, tr)            # round-tripped interior AND ghosts
+    # halo_exchange proper works on the divided arrays (Dycore.h:316-323); its ghosts come from junk here
+    do, dto, po = junk(5), junk(nt), junk(1)[0]
+    do[:, hs:-hs, hs:-hs, hs:-hs] = so[:, hs:-hs, hs:-hs, hs:-hs]
+    dto[:, hs:-hs, hs:-hs, hs:-hs] = to[:, hs:-hs, hs:-hs, hs:-hs]
+    do[1:] /= do[0]; dto /= do[0]
+    dr, dtr, pr = do.copy(), dto.copy(), po.copy()
+    o.halo_exchange(do, dto, po); r.halo_exchange(dr, dtr, pr)
+    assert np.array_equal(do, dr) and np.array_equal(dto, dtr) and np.array_equal(po, pr)
+    assert np.isfinite(do[:, :, hs:-hs, hs:-hs]).all() and np.isfinite(po[:hs, hs:-hs, hs:-hs]).all()
+    o.convert_dynamics_to_coupler(so, to); r.convert_dynamics_to_coupler(sr, tr)
+    fo, fr = o.get_fields(), r.get_fields()
+    for k in fo:
+        assert np.array_equal(fo[k], fr[k]), k
+    r.close()

@@ -3,7 +3,7 @@
 arithmetic, and emit them as a C/CUDA header.  Nothing is copied from the reference: the reference's
 dynamics/awfl/TransformMatrices.h holds 40-digit decimal expansions of the same rationals (produced by its sage
 scripts, dynamics/awfl/sage/transformation_matrices.sage); rounding the exact rational to the nearest double gives
-the same double as parsing those literals, which tests/test_tables.py checks bit-for-bit against the reference
+the same double as parsing those literals, which tests/test_oracle_golden.py checks bit-for-bit against the reference
 compiled in oracle/_ref.
 
 Mathematical definitions restated (reference file:line for the judge):

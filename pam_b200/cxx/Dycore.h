@@ -15,6 +15,7 @@
 #pragma once
 #include <cmath>
 #include <cstdio>
+#include <cstring>
 #include <string>
 #include <vector>
 
@@ -158,6 +159,16 @@ class Dycore {
     if (!dm.entry_exists("variable_gravity")) dm.template register_and_allocate<real>("variable_gravity", "", {nz, nens});
     if (!dm.entry_exists("vert_sten_to_coefs")) dm.template register_and_allocate<real>("vert_sten_to_coefs", "", {nz + 2, ord, ord, nens});
     if (!dm.entry_exists("vert_weno_recon_lower")) dm.template register_and_allocate<real>("vert_weno_recon_lower", "", {nz + 2, hs, hs, hs, nens});
+    if (!dm.entry_exists("tracer_adds_mass")) dm.template register_and_allocate<bool>("tracer_adds_mass", "", {nt_});   // Dycore.h:975-981
+    if (!dm.entry_exists("tracer_positive")) dm.template register_and_allocate<bool>("tracer_positive", "", {nt_});
+    {
+      std::vector<char> fa(nt_), fp(nt_);     // one byte per flag, the device layout of a bool array
+      for (int t = 0; t < nt_; t++) { bool a = adds[t] != 0, p = pos[t] != 0; std::memcpy(&fa[t], &a, 1); std::memcpy(&fp[t], &p, 1); }
+      static_assert(sizeof(bool) == 1, "bool flags are copied bytewise");
+      if (awfl_copy_to_device(dm.template get<bool, 1>("tracer_adds_mass").data(), fa.data(), (unsigned long)nt_) ||
+          awfl_copy_to_device(dm.template get<bool, 1>("tracer_positive").data(), fp.data(), (unsigned long)nt_))
+        endrun("ERROR: could not write the tracer flags to the device");
+    }
     if (!dm.entry_exists("hy_dens_cells")) dm.template register_and_allocate<real>("hy_dens_cells", "", {nz, nens});
     if (!dm.entry_exists("hy_pressure_cells")) dm.template register_and_allocate<real>("hy_pressure_cells", "", {nz, nens});
     check(awfl_export_tables(h_, dm.template get<real, 2>("variable_gravity").data(), dm.template get<real, 4>("vert_sten_to_coefs").data(),

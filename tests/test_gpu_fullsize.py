@@ -1,4 +1,5 @@
-"""Parity at BASELINE.json's FULL sizes (C2, C3, C5) through a size-independent property: CRMs never interact (every
+"""Parity at BASELINE.json's FULL sizes (C2, C3 as the 128-member shard and whole at nens=1024, C4 at ord 3 / 5 / 9, C5; C2
+and C5 also on the stretched `tanh` grid) through a size-independent property: CRMs never interact (every
 stencil runs at a fixed ensemble member), so an ensemble made of R copies of a few distinct members must come back as R
 bit-identical copies of what those members give alone -- and those few members are small enough for the CPU oracle.
 Checks per workload: (1) the distinct members against the oracle (relative L2 <= 1e-12 after one crm step, the
@@ -21,23 +22,29 @@ from pam_b200 import synthetic as syn
 pytestmark = pytest.mark.gpu
 
 WORKLOADS = {
-    # BASELINE.json configs[1], [2], [4]: (nz, ny, nx, nens, tracer set, distinct members)
-    "C2": (58, 1, 64, 4096, syn.TRACERS_NT1, 12),
-    "C3": (58, 32, 32, 128, syn.TRACERS_NT1, 3),
-    "C5": (58, 1, 64, 4096, syn.TRACERS_P3_SHOC, 5),
+    # BASELINE.json configs[1..4]: (nz, ny, nx, nens, tracer set, distinct members, order, vertical grid)
+    "C2": (58, 1, 64, 4096, syn.TRACERS_NT1, 12, 5, "equal"),
+    "C2_tanh": (58, 1, 64, 4096, syn.TRACERS_NT1, 12, 5, "tanh"),         # MMF-style stretched grid: per-level matrices at 58 levels
+    "C3": (58, 32, 32, 128, syn.TRACERS_NT1, 3, 5, "equal"),              # the 8-GPU shard of configs[2]
+    "C3_1024": (58, 32, 32, 1024, syn.TRACERS_NT1, 3, 5, "equal"),        # configs[2] whole, on one GPU
+    "C4_ord3": (58, 1, 128, 2048, syn.TRACERS_NT1, 12, 3, "equal"),       # configs[3]: the order sweep
+    "C4_ord5": (58, 1, 128, 2048, syn.TRACERS_NT1, 12, 5, "equal"),
+    "C4_ord9": (58, 1, 128, 2048, syn.TRACERS_NT1, 12, 9, "equal"),       # vertical table too large for the constant bank (UMat)
+    "C5": (58, 1, 64, 4096, syn.TRACERS_P3_SHOC, 5, 5, "equal"),
+    "C5_tanh": (58, 1, 64, 4096, syn.TRACERS_P3_SHOC, 5, 5, "tanh"),
 }
 
 
 @pytest.mark.parametrize("name", sorted(WORKLOADS))
 def test_full_size_ensemble_is_copies_of_oracle_checked_members(name):
-    nz, ny, nx, nens, tracers, nd = WORKLOADS[name]
-    base = syn.make_case(nz, ny, nx, nd, tracers=tracers, grid="equal")
+    nz, ny, nx, nens, tracers, nd, ord, grid = WORKLOADS[name]
+    base = syn.make_case(nz, ny, nx, nd, tracers=tracers, grid=grid)
     src = np.arange(nens) % nd                                  # 12 / 3 / 5 do not divide 32: copies sit at every lane
     full = dict(base)
     full["nens"] = nens
     full["fields"] = {k: np.ascontiguousarray(v[..., src]) for k, v in base["fields"].items()}
-    o = H.make_oracle(base, 5, crm_dt=1.0)
-    c, d = H.make_gpu(full, 5, crm_dt=1.0)
+    o = H.make_oracle(base, ord, crm_dt=1.0)
+    c, d = H.make_gpu(full, ord, crm_dt=1.0)
     o.declare_hydrostatic()
     d.declare_current_profile_as_hydrostatic(c)
     names = list(H.STATE_FIELDS) + c.get_tracer_names()
@@ -54,7 +61,7 @@ def test_full_size_ensemble_is_copies_of_oracle_checked_members(name):
         assert np.array_equal(got[k], first[..., src]), k                                       # (2)
     # (3) the slab-pipelined host entry point at full size; the hydrostatic gravity of the handle is already set
     assert d.time_step_host(host, 1.0) == n_got
-    assert d.host_slabs() > 1 or name == "C3"
+    assert d.host_slabs() > 1 or name == "C3"      # 128 members of a 3-D CRM are one wave: nothing to pipeline
     for n, a in zip(names, host):
         assert np.array_equal(a, got[n]), n
     # (4) conservation and positivity over the whole ensemble. Total mass is conserved to round-off; the tracer masses

@@ -135,28 +135,48 @@ def test_one_step_matches_oracle(cfg):
             assert got[n].min() >= 0.0
 
 
-def test_hundred_steps_match_oracle_and_conserve_mass():
-    case = _case(nz=12, nx=12, nens=8)
-    o = H.make_oracle(case, 5, crm_dt=1.0)
-    c, d = H.make_gpu(case, 5, crm_dt=1.0)
+@pytest.mark.parametrize("cfg", [
+    dict(ord=5),                                         # 2-D, NT=1
+    dict(ord=5, ny=6, nx=8, nz=10),                      # 3-D
+    dict(ord=5, nt=10),                                  # P3+SHOC tracer set: FCT limiting active every stage
+    dict(ord=3), dict(ord=7), dict(ord=9),               # the other reconstruction orders
+    dict(ord=5, per_ens=True),                           # member-dependent vertical grid (strided per-level matrices)
+    dict(ord=5, grid="equal", nt=10, ny=5, nx=6, nz=8),  # 3-D with the two-kernel FCT path
+])
+def test_hundred_steps_match_oracle_and_conserve_mass(cfg):
+    """north_star: relative L2 of every prognostic field <= 1e-9 after 100 steps, dry mass conserved to round-off. The CUDA
+    path re-associates (row-form WENO, common-denominator weights), takes reciprocals by MUFU seed + Newton and x^gamma as
+    exp(gamma log x); this is where their accumulated effect over 100 x ncycles x 3 stages is bounded, per configuration."""
+    cfg = dict(cfg)
+    ord = cfg.pop("ord")
+    cfg.setdefault("nz", 12); cfg.setdefault("nx", 12); cfg.setdefault("nens", 8)
+    case = _case(**cfg)
+    o = H.make_oracle(case, ord, crm_dt=1.0)
+    c, d = H.make_gpu(case, ord, crm_dt=1.0)
     o.declare_hydrostatic()
     d.declare_current_profile_as_hydrostatic(c)
     m0 = d.compute_mass(c)
     for _ in range(100):
-        o.time_step()
-        d.timeStep(c)
+        assert o.time_step() == d.timeStep(c)
     ref, got = o.get_fields(), H.gpu_fields(c)
     fl = field_floors(ref)
     for k in ref:
         assert rel_l2(got[k], ref[k], fl[k]) <= TOL_100, (k, rel_l2(got[k], ref[k], fl[k]))
     m1 = d.compute_mass(c)
     nt = len(case["tracers"])
-    # total mass (rho*dz mean, row nt) to round-off: 100 steps x 3 stages of FP64 sums
+    # total mass (rho*dz mean, row nt) to round-off: 100 steps x ncycles x 3 stages of FP64 sums
     assert np.max(np.abs(m1[nt] - m0[nt]) / np.abs(m0[nt])) < 1e-13
-    # dry mass = total - sum(adds_mass tracers)
-    dry0 = m0[nt] - sum(m0[i] for i, t in enumerate(case["tracers"]) if t[2])
-    dry1 = m1[nt] - sum(m1[i] for i, t in enumerate(case["tracers"]) if t[2])
-    assert np.max(np.abs(dry1 - dry0) / np.abs(dry0)) < 1e-13
+    m_ref = o.compute_mass()
+    assert np.max(np.abs(m1 - m_ref) / (np.abs(m_ref) + 1e-300)) < 1e-9
+    if nt == 1:
+        # dry mass = total - sum(adds_mass tracers). (With the 10-tracer set the reference ALGORITHM's clip of negative tracer
+        # values is not conservative -- DESIGN.md 2 -- so there the tracer masses are compared with the oracle's above.)
+        dry0 = m0[nt] - sum(m0[i] for i, t in enumerate(case["tracers"]) if t[2])
+        dry1 = m1[nt] - sum(m1[i] for i, t in enumerate(case["tracers"]) if t[2])
+        assert np.max(np.abs(dry1 - dry0) / np.abs(dry0)) < 1e-13
+    for (n, pos, adds) in case["tracers"]:
+        if pos:
+            assert got[n].min() >= 0.0
 
 
 def test_use_gcm_columns_hydrostatic():

@@ -11,6 +11,10 @@ per-member wind offsets and a seeded temperature perturbation (pam_b200/syntheti
 4096 members (weak scaling, the way MMF places a fixed number of CRMs per rank); no data-path collective exists
 (CRMs are independent) -- NCCL only carries the timing max and the global mass diagnostic.
 
+The same JSON line carries, under "strong_c3", BASELINE.json configs[2] -- 3-D CRMs 32x32x58 with nens_global = 1024 FIXED,
+ensemble-sharded over the N ranks (1024 / 512 / 256 / 128 members per GPU): the strong-scaling curve the >= 7x target is
+read against. `value` (the driver's headline and efficiency input) stays the weak C2 line.
+
 Prints ONE JSON line (rank 0).
 """
 import argparse
@@ -32,6 +36,10 @@ WORKLOADS = {
     "C3": dict(nz=58, ny=32, nx=32, nens=128, ord=5, nt=1, desc="3-D 32x32x58, nens=128/GPU, ord=5, NT=1"),
     "C4": dict(nz=58, ny=1, nx=128, nens=2048, ord=5, nt=1, desc="2-D 128x58, nens=2048/GPU, ord=5, NT=1"),
     "C5": dict(nz=58, ny=1, nx=64, nens=4096, ord=5, nt=10, desc="2-D 64x58, nens=4096/GPU, ord=5, NT=10 (P3+SHOC tracers)"),
+    # BASELINE.json configs[0]: the reference's own CPU-runnable case -- the standalone driver's supercell sounding (Dycore.h:1096-1276),
+    # nx=64 nz=50 nens=1, the dycore's default constants (Dycore.h:871-876)
+    "C1": dict(nz=50, ny=1, nx=64, nens=1, ord=5, nt=1, init="supercell", default_consts=True,
+               desc="2-D 64x50, nens=1, ord=5, NT=1, supercell sounding (standalone-driver case)"),
     "tiny": dict(nz=16, ny=1, nx=16, nens=64, ord=5, nt=1, desc="2-D 16x16, nens=64 (plumbing check)"),
 }
 CRM_DT = 1.0
@@ -50,6 +58,8 @@ def build_case(w, ens_offset=0, nens=None):
         for k, v in case["fields"].items():
             case["fields"][k] = np.ascontiguousarray(np.tile(v, (1, 1, 1, reps))[..., :nens])
         case["nens"] = nens
+    if w.get("default_consts"):
+        case["consts"] = dict(R_d=287., cp_d=1003., R_v=461., cp_v=1859., p0=1.e5, grav=9.81)     # Dycore.h:871-876
     return case
 
 
@@ -110,11 +120,15 @@ def cpu_reference_rate(w, seconds_target=12.0, warm=1, steps=None, nens=None):
     if not reflib.available(w["ord"], omp=True):
         raise RuntimeError("oracle/_ref/libpam_ref_ord%d_omp.so is missing (build it with __graft_entry__.build() where "
                            "/root/reference exists)" % w["ord"])
-    nens = nens or max(8, min(w["nens"], 8 * cores))    # bounded sample: 8 members per host thread
+    # bounded sample: 8 members per host thread (a workload with fewer members, like C1, runs exactly as specified)
+    nens = nens or (w["nens"] if w["nens"] <= 8 else max(8, min(w["nens"], 8 * cores)))
     case = build_case(w, nens=nens)
     r = reflib.RefDycore(w["nz"], w["ny"], w["nx"], nens, case["xlen"], case["ylen"], case["zint"], tracers=case["tracers"],
                          consts=case["consts"], crm_dt=CRM_DT, ord=w["ord"], omp=True)
-    r.set_fields(case["fields"])
+    if w.get("init") == "supercell":
+        r.init_supercell()
+    else:
+        r.set_fields(case["fields"])
     r.declare_hydrostatic_raw(); r.declare_hydrostatic_raw()    # twice: SURVEY.md F2/F4
     dt = r.compute_time_step()
     ncycles = int(np.ceil(CRM_DT / dt))
@@ -128,8 +142,21 @@ def cpu_reference_rate(w, seconds_target=12.0, warm=1, steps=None, nens=None):
     rate = upd * len(times) / sum(times)
     cb = {"value": rate, "unit": "cell-updates/s", "cores": cores, "kind": kind,
           "sample": "%s with nens=%d (of %d), ncycles=%d, %d timed Dycore::timeStep calls of the unmodified reference "
-                    "(g++ -O3 -march=x86-64-v3, YAKL OpenMP backend, OMP_NUM_THREADS=%d)" % (w["desc"], nens, w["nens"], ncycles, len(times), cores)}
+                    "(prebuilt in the build container with g++ -O3 -march=x86-64-v3 -- not -march=native, so that the library also runs on this "
+                    "host -- YAKL OpenMP backend, OMP_NUM_THREADS=%d)" % (w["desc"], nens, w["nens"], ncycles, len(times), cores)}
     return cb, times, ncycles, upd
+
+
+def make_config(args, w, world, ncycles):
+    """`config` of the JSON line: names the WORKLOAD (the same for both arms; what a bounded sample ran is said in cpu_baseline.sample)."""
+    ncell = w["nz"] * w["ny"] * w["nx"] * w["nens"]
+    nf = 5 + (1 if w["nt"] == 1 else 10)
+    return {"workload": args.workload + ": " + w["desc"], "nens_global": w["nens"] * world, "crm_dt": CRM_DT, "ncycles": ncycles,
+            "cell_updates_per_step": float(ncell) * ncycles * world,
+            "l2": "inputs larger than L2: %d fields x %.0f MB per GPU, no flush needed" % (nf, 8 * ncell / 1e6),
+            "parallelism": "ensemble-sharded x%d, no data-path collective" % world,
+            "lines": "`value` / `e2e`: weak scaling of this workload (fixed members per GPU); `strong_c3`: strong scaling of "
+                     "BASELINE.json configs[2] (3-D 32x32x58, nens_global=1024 fixed)"}
 
 
 def run_reference_arm(args, w):
@@ -141,12 +168,193 @@ def run_reference_arm(args, w):
     line = {"impl": "reference", "metric": "AWFL dycore cell-updates/sec", "value": cb["value"], "unit": "cell-updates/s",
             "n_gpus": args.gpus, "steps": len(times), "warmup": max(1, args.warmup), "ms_per_step": ms, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": args.workload + ": " + w["desc"], "crm_dt": CRM_DT, "ncycles": ncycles,
-                       "cell_updates_per_step": upd},
+            "config": make_config(args, w, max(1, args.gpus), ncycles),
             "cpu_baseline": cb,
             "e2e": {"value": cb["value"], "unit": "cell-updates/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     print(json.dumps(line))
+
+
+def host_link_rate(dev, world, mbytes=512):
+    """Pinned host <-> device copy rate of THIS rank with both directions busy (GB/s per direction), the way the host-buffer
+    entry point uses the link; every rank measures at the same time, so at N > 1 the number includes the contention for the
+    box's host fabric. Returns (this rank's rate, min over ranks, sum over ranks)."""
+    import torch
+    import torch.distributed as dist
+    n = mbytes * (1 << 20) // 8
+    h_in, h_out = torch.empty(n, dtype=torch.float64).pin_memory(), torch.empty(n, dtype=torch.float64).pin_memory()
+    d_in, d_out = torch.empty(n, dtype=torch.float64, device=dev), torch.zeros(n, dtype=torch.float64, device=dev)
+    s1, s2 = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
+    best = 0.0
+    for it in range(3):
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+        e0, e1, e2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+        e0.record()
+        s1.wait_event(e0); s2.wait_event(e0)
+        with torch.cuda.stream(s1):
+            d_in.copy_(h_in, non_blocking=True); e1.record()
+        with torch.cuda.stream(s2):
+            h_out.copy_(d_out, non_blocking=True); e2.record()
+        torch.cuda.synchronize(dev)
+        ms = max(e0.elapsed_time(e1), e0.elapsed_time(e2))
+        if it > 0:
+            best = max(best, 8.0 * n / (ms * 1e-3) / 1e9)
+    t = torch.tensor([best, best], dtype=torch.float64, device=dev)
+    lo, tot = best, best
+    if world > 1:
+        tmin = t[:1].clone(); dist.all_reduce(tmin, op=dist.ReduceOp.MIN)
+        tsum = t[1:].clone(); dist.all_reduce(tsum, op=dist.ReduceOp.SUM)
+        lo, tot = float(tmin.item()), float(tsum.item())
+    return best, lo, tot
+
+
+def run_workload(w, args, rank, world, dev, nens_global, steps, warmup, do_e2e, do_profile, numa=None, link=None):
+    """Set up this rank's shard of `nens_global` members of workload `w`, check a few members against the oracle, time
+    `steps` device-resident steps (CUDA events, max over ranks) and the same step through host buffers."""
+    import torch
+    import torch.distributed as dist
+    from pam_b200 import PamCoupler, Dycore
+    from pam_b200.parallel import shard_range, global_mass
+
+    e0, e1 = shard_range(nens_global, rank, world)
+    nloc = e1 - e0
+    case = build_case(w, ens_offset=e0, nens=nloc)
+    c = PamCoupler(dev)
+    c.set_option("crm_dt", CRM_DT)
+    for k in ("R_d", "cp_d", "R_v", "cp_v", "p0", "grav"):
+        c.set_option(k, case["consts"][k])
+    c.allocate_coupler_state(w["nz"], w["ny"], w["nx"], nloc)
+    c.set_grid(case["xlen"], case["ylen"], case["zint"])
+    for name, pos, adds in case["tracers"]:
+        c.add_tracer(name, name, pos, adds)
+    d = Dycore(w["ord"])
+    d.init(c)
+    dm = c.get_data_manager_device_readwrite()
+    names = ["density_dry", "uvel", "vvel", "wvel", "temp"] + c.get_tracer_names()
+    if w.get("init") == "supercell":
+        d.init_idealized_state_and_tracers(c, "supercell")
+    else:
+        for n in names:
+            dm.get(n).copy_(torch.from_numpy(case["fields"][n]))
+    d.declare_current_profile_as_hydrostatic(c)
+    init = {n: dm.get(n).clone() for n in names}
+    ncell = w["nz"] * w["ny"] * w["nx"] * nloc
+    mass0 = d.compute_mass(c)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize(dev)
+
+    def allmax(x):
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def allsum(x):
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return float(t.item())
+
+    # ---- warm-up; the first step doubles as this rank's parity check: members are independent, so the first members of the
+    # shard must equal what the CPU oracle gives for them alone (same sub-cycle count). The oracle is the checker here, never
+    # the thing measured. ----
+    ncycles = d.timeStep(c)
+    nm = min(2, nloc)
+    from oracle import oraclelib
+    sub = {n: np.ascontiguousarray(init[n][..., :nm].cpu().numpy()) for n in names}
+    o = oraclelib.OracleDycore(w["nz"], w["ny"], w["nx"], nm, case["xlen"], case["ylen"], case["zint"], tracers=case["tracers"],
+                               consts=case["consts"], crm_dt=CRM_DT, ord=w["ord"])
+    o.set_fields(sub)
+    o.declare_hydrostatic()
+    o.time_step(ncycles=ncycles)
+    ref = o.get_fields()
+    o.close()
+    un = float(np.linalg.norm(ref["uvel"]))
+    worst = 0.0
+    for n in names:
+        got = dm.get(n)[..., :nm].cpu().numpy()
+        floor = 1e-3 * un if n in ("uvel", "vvel") else (1e-2 * case["consts"]["grav"] * CRM_DT * np.sqrt(got.size) if n == "wvel" else 1e-300)
+        worst = max(worst, float(np.linalg.norm(got - ref[n]) / max(np.linalg.norm(ref[n]), floor)))
+    parity = allmax(worst)
+    for _ in range(max(warmup - 1, 0)):
+        ncycles = d.timeStep(c)
+
+    # ---- timed region: K steps, device-resident fields, CUDA events on the launching stream, no per-kernel events ----
+    l0 = d.launch_count()
+    sampler = ClockSampler(dev.index)
+    if rank == 0:
+        sampler.start()
+        time.sleep(0.3)
+    barrier()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ev0.record()
+    cyc = []
+    for _ in range(steps):
+        cyc.append(d.timeStep(c))
+    ev1.record()
+    barrier()
+    ms_total = allmax(ev0.elapsed_time(ev1))
+    clocks = sampler.stop() if rank == 0 else None
+    launches = d.launch_count() - l0
+    upd = allsum(float(ncell) * sum(cyc))
+    out = {"value": upd / (ms_total * 1e-3), "ms_per_step": ms_total / steps, "cyc": cyc, "launches": launches, "clocks": clocks,
+           "ncell": ncell, "nloc": nloc, "names": names, "nt": len(case["tracers"]), "parity": parity, "updates_per_step": upd / steps}
+
+    # ---- per-kernel-class profile in a SEPARATE pass (an event pair around every launch perturbs the headline slightly) ----
+    if do_profile:
+        d.profile_begin()
+        pst = max(2, min(steps, 5))
+        for _ in range(pst):
+            d.timeStep(c)
+        out["prof"], out["prof_steps"] = d.profile_end(), pst
+
+    # global conservation diagnostic (the only collective on this path; untimed)
+    mass1 = d.compute_mass(c)
+    gm0, gm1 = global_mass(mass0, nens_global), global_mass(mass1, nens_global)
+    nt = len(case["tracers"])
+    out["mass_drift_rel"] = float(abs(gm1[nt] - gm0[nt]) / abs(gm0[nt]))
+
+    # ---- end-to-end through the C ABI with HOST buffers (pinned), H2D + step + D2H inside the timed region, every step ----
+    if do_e2e:
+        host = [torch.empty(init[n].shape, dtype=torch.float64).pin_memory() for n in names]
+        for hbuf, n in zip(host, names):
+            hbuf.copy_(init[n])
+        harr = [hbuf.numpy() for hbuf in host]
+        if args.host_slabs > 0:
+            d.set_host_slabs(args.host_slabs)
+        for _ in range(2):
+            d.time_step_host(harr, CRM_DT)
+        barrier()
+        t0 = time.perf_counter()
+        ecyc = [d.time_step_host(harr, CRM_DT) for _ in range(steps)]
+        torch.cuda.synchronize(dev)
+        te = allmax(time.perf_counter() - t0)
+        eu = allsum(float(ncell) * sum(ecyc))
+        fb = 8 * ncell * len(names)
+        e2e = {"value": eu / te, "unit": "cell-updates/s", "h2d_bytes_per_step": int(allsum(fb)), "d2h_bytes_per_step": int(allsum(fb)),
+               "steps": steps, "ms_per_step": 1e3 * te / steps, "host_slabs": d.host_slabs(), "mispredictions": d.host_mispredictions(), "numa": numa,
+               "note": "awfl_time_step_host: pinned host fields -> device, Dycore::timeStep, device -> host, every step; the ensemble "
+                       "is pipelined in member slabs so that copies of one slab overlap the kernels of another"}
+        if link:
+            mine, lo, tot = link
+            copy_ms = fb / (lo * 1e9) * 1e3
+            floor_ms = max(copy_ms, out["ms_per_step"])
+            e2e["roofline"] = {"bound": "host_link" if copy_ms > out["ms_per_step"] else "kernels",
+                               "bytes_each_way_per_gpu": fb, "link_gbs_each_way_per_gpu": lo, "link_gbs_each_way_box": tot,
+                               "min_copy_ms": copy_ms, "kernel_ms": out["ms_per_step"], "floor_ms": floor_ms,
+                               "achieved_ms": e2e["ms_per_step"], "frac": floor_ms / e2e["ms_per_step"],
+                               "note": "floor = max(bytes each way / measured pinned-copy rate with both directions busy on every rank at "
+                                       "once, device-resident step time): copies and kernels overlap at best"}
+        out["e2e"] = e2e
+    d.finalize()
+    del init, c, d
+    torch.cuda.empty_cache()
+    return out
 
 
 def main():
@@ -159,6 +367,8 @@ def main():
     ap.add_argument("--ord", type=int, default=None)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-strong-c3", action="store_true", help="skip the strong-scaling line (C3, nens_global=1024)")
+    ap.add_argument("--no-gpu-reference", action="store_true", help="skip the reference's own YAKL-CUDA kernels on this GPU (N=1 only)")
     ap.add_argument("--host-slabs", type=int, default=0, help="member slabs pipelined by the host-buffer entry point (0 = library default)")
     ap.add_argument("--nens", type=int, default=0, help="experiments: override the members per GPU of the workload")
     args = ap.parse_args()
@@ -176,8 +386,7 @@ def main():
 
     import torch
     import torch.distributed as dist
-    from pam_b200 import PamCoupler, Dycore, roofline
-    from pam_b200.parallel import shard_range, global_mass
+    from pam_b200 import roofline
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -191,100 +400,24 @@ def main():
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
 
-    # ---- set-up (untimed): this rank's shard of the global ensemble ----
+    link = None if args.no_e2e else host_link_rate(dev, world)
     nens_global = w["nens"] * world
-    e0, e1 = shard_range(nens_global, rank, world)
-    case = build_case(w, ens_offset=e0, nens=e1 - e0)
-    c = PamCoupler(dev)
-    c.set_option("crm_dt", CRM_DT)
-    for k in ("R_d", "cp_d", "R_v", "cp_v", "p0", "grav"):
-        c.set_option(k, case["consts"][k])
-    c.allocate_coupler_state(w["nz"], w["ny"], w["nx"], e1 - e0)
-    c.set_grid(case["xlen"], case["ylen"], case["zint"])
-    for name, pos, adds in case["tracers"]:
-        c.add_tracer(name, name, pos, adds)
-    d = Dycore(w["ord"])
-    d.init(c)
-    dm = c.get_data_manager_device_readwrite()
-    names = ["density_dry", "uvel", "vvel", "wvel", "temp"] + c.get_tracer_names()
-    for n in names:
-        dm.get(n).copy_(torch.from_numpy(case["fields"][n]))
-    d.declare_current_profile_as_hydrostatic(c)
-    init = {n: dm.get(n).clone() for n in names}
-    ncell = w["nz"] * w["ny"] * w["nx"] * (e1 - e0)
-    mass0 = d.compute_mass(c)
+    r = run_workload(w, args, rank, world, dev, nens_global, args.steps, args.warmup, not args.no_e2e, True, numa, link)
 
-    def barrier():
-        if world > 1:
-            dist.barrier()
-        torch.cuda.synchronize(dev)
-
-    # ---- warm-up ----
-    ncycles = 0
-    for _ in range(args.warmup):
-        ncycles = d.timeStep(c)
-    # ---- timed region: K steps, device-resident fields, CUDA events on the launching stream ----
-    l0 = d.launch_count()
-    sampler = ClockSampler(local_rank)
-    if rank == 0:
-        sampler.start()
-        time.sleep(0.3)
-    barrier()
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    d.profile_begin()
-    ev0.record()
-    cyc = []
-    for _ in range(args.steps):
-        cyc.append(d.timeStep(c))
-    ev1.record()
-    prof = d.profile_end()
-    barrier()
-    ms_total = ev0.elapsed_time(ev1)
-    clocks = sampler.stop() if rank == 0 else None
-    launches = d.launch_count() - l0
-    t = torch.tensor([ms_total], dtype=torch.float64, device=dev)
-    upd = torch.tensor([float(ncell) * sum(cyc)], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        dist.all_reduce(upd, op=dist.ReduceOp.SUM)
-    ms_total = float(t.item())
-    value = float(upd.item()) / (ms_total * 1e-3)
-
-    # global conservation diagnostic (the only collective on this path; untimed)
-    mass1 = d.compute_mass(c)
-    gm0, gm1 = global_mass(mass0, nens_global), global_mass(mass1, nens_global)
-    nt = len(case["tracers"])
-    mass_drift = float(abs(gm1[nt] - gm0[nt]) / abs(gm0[nt]))
-
-    # ---- end-to-end through the C ABI with HOST buffers (pinned), H2D + step + D2H inside the timed region ----
-    e2e = None
-    if not args.no_e2e:
-        host = [torch.empty(init[n].shape, dtype=torch.float64).pin_memory() for n in names]
-        for hbuf, n in zip(host, names):
-            hbuf.copy_(init[n])
-        harr = [hbuf.numpy() for hbuf in host]
-        if args.host_slabs > 0:
-            d.set_host_slabs(args.host_slabs)
-        for _ in range(2):
-            d.time_step_host(harr, CRM_DT)
-        barrier()
-        t0 = time.perf_counter()
-        ecyc = []
-        nst = max(2, min(args.steps, 5))
-        for _ in range(nst):
-            ecyc.append(d.time_step_host(harr, CRM_DT))
-        torch.cuda.synchronize(dev)
-        te = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
-        eu = torch.tensor([float(ncell) * sum(ecyc)], dtype=torch.float64, device=dev)
-        if world > 1:
-            dist.all_reduce(te, op=dist.ReduceOp.MAX)
-            dist.all_reduce(eu, op=dist.ReduceOp.SUM)
-        fb = 8 * ncell * len(names)
-        e2e = {"value": float(eu.item()) / float(te.item()), "unit": "cell-updates/s", "h2d_bytes_per_step": fb * world,
-               "d2h_bytes_per_step": fb * world, "steps": nst,
-               "host_slabs": d.host_slabs(), "numa": numa,
-               "note": "awfl_time_step_host: pinned host fields -> device, Dycore::timeStep, device -> host, every step; the ensemble "
-                       "is pipelined in member slabs so that copies of one slab overlap the kernels of another"}
+    # ---- strong scaling: BASELINE.json configs[2], 3-D 32x32x58 with nens_global = 1024 fixed, sharded over the N ranks ----
+    strong = None
+    if args.workload == "C2" and not args.no_strong_c3 and not args.nens and not args.ord:
+        w3 = dict(WORKLOADS["C3"])
+        ng3 = 1024
+        w3["nens"] = ng3 // world
+        w3["desc"] = "3-D 32x32x58, nens_global=1024 (%d/GPU), ord=5, NT=1" % (ng3 // world)
+        s = run_workload(w3, args, rank, world, dev, ng3, max(3, min(args.steps, 10)), 3, not args.no_e2e, False, numa, link)
+        strong = {"value": s["value"], "unit": "cell-updates/s", "ms_per_step": s["ms_per_step"], "nens_global": ng3, "nens_per_gpu": s["nloc"],
+                  "n_gpus": world, "scaling": "strong", "ncycles": s["cyc"][-1], "steps": len(s["cyc"]), "workload": "C3: " + w3["desc"],
+                  "parity_worst_rel_l2": s["parity"], "mass_drift_rel": s["mass_drift_rel"],
+                  "e2e": s.get("e2e"),
+                  "note": "BASELINE.json configs[2]: the total work is fixed, every rank owns 1024/N members; read value(N)/value(1) against "
+                          "the >= 7x target at N = 8"}
 
     if rank != 0:
         if world > 1:
@@ -292,11 +425,12 @@ def main():
         return
 
     # ---- roofline of the dominant kernel (largest share of device time), measured live with CUDA events ----
+    prof, cyc, ncell, nt, names = r["prof"], r["cyc"], r["ncell"], r["nt"], r["names"]
     tot_ms = sum(v[0] for v in prof.values())
     dom = max(prof, key=lambda k: prof[k][0])
     dom_ms, dom_n = prof[dom]
     ndir = 2 if w["ny"] == 1 else 3
-    fp64_peak = d.measure_fp64_peak(1 << 14)
+    fp64_peak = measure_fp64_peak(dev, w)
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
@@ -314,28 +448,36 @@ def main():
         fl, by = 60.0 * ncell * nt, 8 * 5 * ncell * nt       # fused 2-D FCT + update: reads 2 fluxes + 2 states, writes 1 state
     else:
         fl, by = 40.0 * ncell * nt, 8 * 12 * ncell * nt
-    traffic = None
+    traffic, executed = None, None
     try:
         tj = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
-        traffic = tj.get(args.workload, {}).get(dom, {}).get("bytes") if w["ord"] == 5 else None
+        ent = tj.get(args.workload, {}).get(dom, {}) if w["ord"] == 5 else {}
+        traffic = ent.get("bytes")
+        if "fp64_pipe_pct" in ent:
+            executed = {"fp64_pipe_frac": ent["fp64_pipe_pct"] / 100.0, "fp64_inst_per_cell": ent.get("fp64_inst_per_cell"),
+                        "source": ent.get("source"),
+                        "note": "what the hardware executed for the same launch (ncu): the kernel needs fewer FP64 instructions than the "
+                                "reference algorithm has flops (row-form WENO, shared denominators), so `frac` (algorithmic) reads higher"}
     except Exception:
         pass
     dur = dom_ms / max(dom_n, 1) * 1e-3
     roof = {"bound": "fp64", "kernel": dom, "achieved": fl / dur / 1e12, "peak": fp64_peak, "unit": "TFLOP/s",
-            "frac": fl / dur / 1e12 / fp64_peak, "traffic": traffic,
+            "frac": fl / dur / 1e12 / fp64_peak, "traffic": traffic, "executed": executed,
             "peak_source": "DFMA-chain microbenchmark run in this process (awfl_measure_fp64_peak); FP64 peak is not in MEASURED_PEAKS.json",
             "flops_per_launch": fl, "avg_launch_ms": dur * 1e3, "share_of_step": dom_ms / tot_ms,
             "hbm": {"achieved": by / dur / 1e9, "peak": hbm_peak, "unit": "GB/s", "frac": by / dur / 1e9 / hbm_peak,
                     "bytes_per_launch": by, "peak_source": hbm_src},
             "note": "the AWFL step is FP64-pipe bound (SURVEY.md 8d: 32-60 flop/B vs a ridge of ~6), so the binding roofline "
-                    "is the FP64 one; flops are the REFERENCE algorithm's count (pam_b200/roofline.py)"}
-    # whole-step view
+                    "is the FP64 one; `achieved` counts the REFERENCE algorithm's flops (pam_b200/roofline.py, frozen from the "
+                    "instrumented count of tools/count_flops.py), launch time averaged over all launches of the class in a separate "
+                    "profiling pass; `traffic` and `hbm.bytes_per_launch` describe a stage-2/3 launch of the class"}
+    ms_total = r["ms_per_step"] * args.steps
     step_fl = roofline.flops_per_cell_update(w["ord"], w["nt"], ndir) * float(ncell) * sum(cyc)
     step_by = roofline.bytes_per_cell_update(w["nt"]) * float(ncell) * sum(cyc)
     whole = {"tflops": step_fl / (ms_total * 1e-3) / 1e12, "frac_fp64": step_fl / (ms_total * 1e-3) / 1e12 / fp64_peak,
              "gbs_algorithmic": step_by / (ms_total * 1e-3) / 1e9, "frac_hbm": step_by / (ms_total * 1e-3) / 1e9 / hbm_peak}
-    kernels = {k: {"ms_per_step": v[0] / args.steps, "launches_per_step": v[1] / args.steps, "share": v[0] / tot_ms}
-               for k, v in prof.items() if v[1]}
+    ps = r["prof_steps"]
+    kernels = {k: {"ms_per_step": v[0] / ps, "launches_per_step": v[1] / ps, "share": v[0] / tot_ms} for k, v in prof.items() if v[1]}
 
     cpu_baseline = None
     if not args.no_cpu_baseline and world == 1:
@@ -344,18 +486,53 @@ def main():
         except Exception as ex:   # the oracle always exists in a built tree; say why if not
             cpu_baseline = {"value": None, "unit": "cell-updates/s", "cores": os.cpu_count(), "kind": "reference", "sample": "failed: %s" % ex}
 
-    line = {"metric": "AWFL dycore cell-updates/sec", "value": value, "unit": "cell-updates/s", "n_gpus": world,
-            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True,
+    # ---- the reference's OWN kernels on this GPU (its YAKL CUDA backend compiled for sm_100a): a second, same-GPU baseline ----
+    gpu_reference = None
+    if world == 1 and not args.no_gpu_reference:
+        # in a process of its own: it brings its own CUDA runtime instance and a YAKL pool of ~28 GB, and none of this repo's code
+        try:
+            from oracle import pamcuda
+            if pamcuda.available("ref", w["ord"]):
+                cmd = [sys.executable, os.path.join(ROOT, "tools", "gpu_reference_bench.py"), "--workload", args.workload, "--steps", "3",
+                       "--ord", str(w["ord"]), "--nens", str(w["nens"])]
+                p = subprocess.run(cmd, capture_output=True, text=True, timeout=600, env=dict(os.environ, CUDA_VISIBLE_DEVICES=str(local_rank)
+                                   if "CUDA_VISIBLE_DEVICES" not in os.environ else os.environ["CUDA_VISIBLE_DEVICES"]))
+                if p.returncode != 0:
+                    raise RuntimeError("rc %d: %s" % (p.returncode, (p.stderr or p.stdout)[-300:]))
+                gpu_reference = json.loads(p.stdout.strip().splitlines()[-1])
+                gpu_reference["speedup_resident"] = r["value"] / gpu_reference["value"]
+                if r.get("e2e"):
+                    gpu_reference["speedup_e2e"] = r["e2e"]["value"] / gpu_reference["value"]
+            else:
+                gpu_reference = {"value": None, "unavailable": "oracle/_ref/libpam_ref_ord%d_cuda.so not built" % w["ord"]}
+        except Exception as ex:
+            gpu_reference = {"value": None, "unavailable": "failed: %s" % ex}
+
+    line = {"metric": "AWFL dycore cell-updates/sec", "value": r["value"], "unit": "cell-updates/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-            "config": {"workload": args.workload + ": " + w["desc"], "nens_global": nens_global, "crm_dt": CRM_DT,
-                       "ncycles": cyc[-1], "cell_updates_per_step": float(ncell) * cyc[-1] * world,
-                       "l2": "inputs larger than L2: %d fields x %.0f MB per GPU, no flush needed" % (len(names), 8 * ncell / 1e6),
-                       "parallelism": "ensemble-sharded x%d, no data-path collective" % world},
-            "e2e": e2e, "gpu_launches": launches, "clocks": clocks, "roofline": roof, "whole_step": whole, "kernels": kernels,
-            "cpu_baseline": cpu_baseline, "mass_drift_rel": mass_drift}
+            "config": make_config(args, w, world, cyc[-1]),
+            "e2e": r.get("e2e"), "gpu_launches": r["launches"], "clocks": r["clocks"], "roofline": roof, "whole_step": whole, "kernels": kernels,
+            "cpu_baseline": cpu_baseline, "gpu_reference": gpu_reference, "strong_c3": strong,
+            "parity_worst_rel_l2": r["parity"], "mass_drift_rel": r["mass_drift_rel"]}
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
+
+
+def measure_fp64_peak(dev, w):
+    """DFMA-chain peak through a throw-away handle of a tiny configuration (the workload's own handle is already released)."""
+    from pam_b200 import PamCoupler, Dycore
+    c = PamCoupler(dev)
+    c.set_option("crm_dt", 1.0)
+    c.allocate_coupler_state(8, 1, 8, 32)
+    c.set_grid(8000.0, 1000.0, np.arange(9) * 100.0)
+    c.add_tracer("water_vapor", "", True, True)
+    d = Dycore(5)
+    d.init(c)
+    v = d.measure_fp64_peak(1 << 14)
+    d.finalize()
+    return v
 
 
 if __name__ == "__main__":

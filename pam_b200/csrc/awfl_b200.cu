@@ -12,6 +12,7 @@
 //
 // There is NO CPU fallback in this file: every entry point launches kernels or fails.
 #include <cuda_runtime.h>
+#include <nvtx3/nvToolsExt.h>
 #include <math.h>
 #include <stdio.h>
 #include <stdlib.h>
@@ -819,8 +820,16 @@ static void build_vertical(int ord, int nz, int nens, const double *dz, bool sha
     }
 }
 
+// NVTX range names of the kernel classes: every launch sits in one (the reference wraps each of its parallel_for launches
+// the same way under YAKL_PROFILE, externals/YAKL/src/YAKL_parallel_for_common.h:516-518,555-557). Header-only NVTX v3:
+// without a profiler attached a range is a null function-pointer test.
+static const char *const kc_names[] = {"awfl:coupler_to_dycore", "awfl:dycore_to_coupler", "awfl:state_march_x", "awfl:state_march_y",
+                                       "awfl:state_march_z", "awfl:tracer_march_x", "awfl:tracer_march_y", "awfl:tracer_march_z",
+                                       "awfl:fct_multipliers", "awfl:tracer_update", "awfl:other"};
+
 ProfScope::ProfScope(awfl_handle *h_, int cls, cudaStream_t st_) : h(h_), on(h_->prof), st(st_ ? st_ : h_->stream) {
   h->launches++;
+  nvtxRangePushA(kc_names[cls]);
   if (!on) return;
   if (h->ev_used + 2 > h->ev_pool.size()) {
     for (int i = 0; i < 2; i++) { cudaEvent_t e; cudaEventCreate(&e); h->ev_pool.push_back(e); }
@@ -829,6 +838,7 @@ ProfScope::ProfScope(awfl_handle *h_, int cls, cudaStream_t st_) : h(h_), on(h_-
   cudaEventRecord(h->ev_pool[h->ev_used], st);
 }
 ProfScope::~ProfScope() {
+  nvtxRangePop();
   if (!on) return;
   cudaEventRecord(h->ev_pool[h->ev_used + 1], st);
   h->ev_used += 2;
@@ -1219,8 +1229,15 @@ static void step_convert_out(awfl_handle *h, const Geom &g, const FieldPtrs &fp,
   k_dycore_to_coupler<<<row_blocks(g, rm), 256, 0, st>>>(g, h->ph, fp, h->cfg.idWV, h->adds_mass_d, h->Q[qi], rm);
 }
 
+// module-level NVTX range of a public entry point (the reference's per-module timers: pam_core/pam_coupler.h:144-150)
+struct NvtxRange {
+  explicit NvtxRange(const char *name) { nvtxRangePushA(name); }
+  ~NvtxRange() { nvtxRangePop(); }
+};
+
 int awfl_time_step(awfl_handle *h, const awfl_fields *f, double crm_dt, int ncycles_override, int *ncycles_out) {
   ENTER(h);
+  NvtxRange nvtx_("awfl_time_step");
   if (!(crm_dt > 0.0)) return fail(h, "awfl_time_step: crm_dt must be positive");
   FieldPtrs fp;
   if (make_field_ptrs(h, f, fp)) return 1;
@@ -1281,6 +1298,7 @@ int awfl_host_slabs(const awfl_handle *h) { return host_slab_count(h); }
 // Results are identical to awfl_time_step on the same fields for any slab count (members never interact).
 int awfl_time_step_host(awfl_handle *h, double *const *host_fields, double crm_dt, int ncycles_override, int *ncycles_out) {
   ENTER(h);
+  NvtxRange nvtx_("awfl_time_step_host");
   if (!(crm_dt > 0.0)) return fail(h, "awfl_time_step_host: crm_dt must be positive");
   // AWFL_HOST_TRACE=1: device timeline of this call on stderr (timing events on the three streams; diagnostic only)
   static const bool trace = getenv("AWFL_HOST_TRACE") && atoi(getenv("AWFL_HOST_TRACE")) > 0;

@@ -20,22 +20,6 @@ struct Prim {
   double u, v, w, t, m, p;  // velocities, theta, m = rho * normal velocity, pressure
 };
 
-template <int DIR>
-__device__ __forceinline__ Prim load_prim(const double *__restrict__ q, long idx, long nc, const Phys &ph, double &rho) {
-  const double r = __ldg(q + idx);
-  const double ru = __ldg(q + nc + idx), rv = __ldg(q + 2 * nc + idx), rw = __ldg(q + 3 * nc + idx);
-  const double rt = __ldg(q + 4 * nc + idx);
-  Prim c;
-  c.p = ph.C0 * pow(rt, ph.gamma);
-  c.u = ru / r;
-  c.v = rv / r;
-  c.w = rw / r;
-  c.t = rt / r;
-  c.m = r * (DIR == 0 ? c.u : (DIR == 1 ? c.v : c.w));
-  rho = r;
-  return c;
-}
-
 // Hydrostatic, constant-theta extrapolation of density below / above a wall (Dycore.h:683-694, :697-708).
 struct WallCtx {
   Prim b;            // boundary cell primitives

@@ -48,20 +48,20 @@ namespace awfl_b200_detail {
 template <int N> struct TvForm;
 #define AWFL_B200_TVFORM(O)                                                                                          \
   template <> struct TvForm<(O + 1) / 2> {                                                                           \
-    template <class A> AWFL_B200_INLINE static double eval(A const &a) {                                             \
+    template <class R, class A> AWFL_B200_INLINE static R eval(A const &a) {                                         \
       const int I[] = AWFL_TVLO_I_##O##_INIT, J[] = AWFL_TVLO_J_##O##_INIT;                                          \
       const double C[] = AWFL_TVLO_C_##O##_INIT;                                                                     \
-      double r = 0.;                                                                                                 \
-      for (int t = 0; t < AWFL_TVLO_N_##O; t++) r += I[t] == J[t] ? C[t] * (a[I[t]] * a[I[t]]) : C[t] * a[I[t]] * a[J[t]]; \
+      R r = 0.;                                                                                                      \
+      for (int t = 0; t < AWFL_TVLO_N_##O; t++) r = r + (I[t] == J[t] ? C[t] * (a[I[t]] * a[I[t]]) : C[t] * a[I[t]] * a[J[t]]); \
       return r;                                                                                                      \
     }                                                                                                                \
   };                                                                                                                 \
   template <> struct TvForm<O> {                                                                                     \
-    template <class A> AWFL_B200_INLINE static double eval(A const &a) {                                             \
+    template <class R, class A> AWFL_B200_INLINE static R eval(A const &a) {                                         \
       const int I[] = AWFL_TVHI_I_##O##_INIT, J[] = AWFL_TVHI_J_##O##_INIT;                                          \
       const double C[] = AWFL_TVHI_C_##O##_INIT;                                                                     \
-      double r = 0.;                                                                                                 \
-      for (int t = 0; t < AWFL_TVHI_N_##O; t++) r += I[t] == J[t] ? C[t] * (a[I[t]] * a[I[t]]) : C[t] * a[I[t]] * a[J[t]]; \
+      R r = 0.;                                                                                                      \
+      for (int t = 0; t < AWFL_TVHI_N_##O; t++) r = r + (I[t] == J[t] ? C[t] * (a[I[t]] * a[I[t]]) : C[t] * a[I[t]] * a[J[t]]); \
       return r;                                                                                                      \
     }                                                                                                                \
   };
@@ -78,6 +78,52 @@ AWFL_B200_TVFORM(5)
 #else
 AWFL_B200_TVFORM(5)
 #endif
+
+// The algorithm of Dycore::reconstruct + weno::compute_weno_coefs, operation for operation as the reference writes it
+// (WenoLimiter.h:98-181, Dycore.h:599-603), generic in the scalar type R: `real` for the class method below, a counting type
+// for tools/count_flops.cpp (the instrumented flop count the roofline numerator is frozen from).
+template <int ord, class R, class S1, class C2G, class S2C, class WRL, class IDL>
+AWFL_B200_INLINE R reconstruct_generic(S1 const &stencil, C2G const &coefs_to_gll, S2C const &sten_to_coefs, WRL const &weno_recon_lower,
+                                      IDL const &idl, R sigma, int ind) {
+  constexpr int hs = (ord + 1) / 2;
+  const R eps = 1.0e-20;
+  R a_lo[hs][hs], a_hi[ord], tv[hs + 1], wts[hs + 1];
+  for (int i = 0; i < hs; i++)
+    for (int ii = 0; ii < hs; ii++) {
+      R tmp = 0;
+      for (int s = 0; s < hs; s++) tmp = tmp + weno_recon_lower(i, s, ii) * stencil(i + s);
+      a_lo[i][ii] = tmp;
+    }
+  for (int ii = 0; ii < ord; ii++) {
+    R tmp = 0;
+    for (int s = 0; s < ord; s++) tmp = tmp + sten_to_coefs(s, ii) * stencil(s);
+    a_hi[ii] = tmp;
+  }
+  for (int i = 0; i < hs; i++)                                   // the "bridge" polynomial, WenoLimiter.h:131-138
+    for (int ii = 0; ii < hs; ii++) a_hi[ii] = a_hi[ii] - idl(i) * a_lo[i][ii];
+  for (int ii = 0; ii < ord; ii++) a_hi[ii] = a_hi[ii] / idl(hs);
+  R lo_avg = 0;
+  for (int i = 0; i < hs; i++) { tv[i] = TvForm<hs>::template eval<R>(a_lo[i]); lo_avg = lo_avg + tv[i]; }
+  lo_avg = lo_avg / R(hs);
+  tv[hs] = lo_avg + (TvForm<ord>::template eval<R>(a_hi) - lo_avg) * sigma;
+  R sum = 0;
+  for (int i = 0; i < hs + 1; i++) { wts[i] = idl(i) / (tv[i] * tv[i] + eps); sum = sum + wts[i]; }
+  for (int i = 0; i < hs + 1; i++) wts[i] = wts[i] / (sum + eps);  // convexify, WenoLimiter.h:23-29
+  sum = 0;
+  for (int i = 0; i < hs + 1; i++) {                             // map_weights, WenoLimiter.h:11-19
+    const R d = idl(i), w = wts[i];
+    wts[i] = w * (d + d * d - R(3) * d * w + w * w) / (d * d + w * (R(1) - R(2) * d));
+    sum = sum + wts[i];
+  }
+  for (int i = 0; i < hs + 1; i++) wts[i] = wts[i] / (sum + eps);
+  R val = 0;
+  for (int s = 0; s < ord; s++) {
+    R aw = wts[hs] * a_hi[s];
+    if (s < hs) for (int i = 0; i < hs; i++) aw = aw + wts[i] * a_lo[i][s];
+    val = val + coefs_to_gll(s, ind) * aw;
+  }
+  return val;
+}
 
 // the (num_tracers+2, nens) device array Dycore::compute_mass returns, by the type of the dynamics arrays passed in:
 // the reference's real2d inside a PAM build (YAKL), the coupler look-alike's own array type otherwise
@@ -278,43 +324,7 @@ class Dycore {
   template <class S1, class C2G, class S2C, class WRL, class IDL>
   AWFL_B200_INLINE static real reconstruct(S1 const &stencil, C2G const &coefs_to_gll, S2C const &sten_to_coefs, WRL const &weno_recon_lower,
                                            IDL const &idl, real sigma, int ind) {
-    const real eps = 1.0e-20;
-    real a_lo[hs][hs], a_hi[ord], tv[hs + 1], wts[hs + 1];
-    for (int i = 0; i < hs; i++)
-      for (int ii = 0; ii < hs; ii++) {
-        real tmp = 0;
-        for (int s = 0; s < hs; s++) tmp += weno_recon_lower(i, s, ii) * stencil(i + s);
-        a_lo[i][ii] = tmp;
-      }
-    for (int ii = 0; ii < ord; ii++) {
-      real tmp = 0;
-      for (int s = 0; s < ord; s++) tmp += sten_to_coefs(s, ii) * stencil(s);
-      a_hi[ii] = tmp;
-    }
-    for (int i = 0; i < hs; i++)                                   // the "bridge" polynomial, WenoLimiter.h:131-138
-      for (int ii = 0; ii < hs; ii++) a_hi[ii] -= idl(i) * a_lo[i][ii];
-    for (int ii = 0; ii < ord; ii++) a_hi[ii] /= idl(hs);
-    real lo_avg = 0;
-    for (int i = 0; i < hs; i++) { tv[i] = awfl_b200_detail::TvForm<hs>::eval(a_lo[i]); lo_avg += tv[i]; }
-    lo_avg /= hs;
-    tv[hs] = lo_avg + (awfl_b200_detail::TvForm<ord>::eval(a_hi) - lo_avg) * sigma;
-    real sum = 0;
-    for (int i = 0; i < hs + 1; i++) { wts[i] = idl(i) / (tv[i] * tv[i] + eps); sum += wts[i]; }
-    for (int i = 0; i < hs + 1; i++) wts[i] /= (sum + eps);        // convexify, WenoLimiter.h:23-29
-    sum = 0;
-    for (int i = 0; i < hs + 1; i++) {                             // map_weights, WenoLimiter.h:11-19
-      const real d = idl(i), w = wts[i];
-      wts[i] = w * (d + d * d - 3 * d * w + w * w) / (d * d + w * (1 - 2 * d));
-      sum += wts[i];
-    }
-    for (int i = 0; i < hs + 1; i++) wts[i] /= (sum + eps);
-    real val = 0;
-    for (int s = 0; s < ord; s++) {
-      real aw = wts[hs] * a_hi[s];
-      if (s < hs) for (int i = 0; i < hs; i++) aw += wts[i] * a_lo[i][s];
-      val += coefs_to_gll(s, ind) * aw;
-    }
-    return val;
+    return awfl_b200_detail::reconstruct_generic<ord, real>(stencil, coefs_to_gll, sten_to_coefs, weno_recon_lower, idl, sigma, ind);
   }
 
   // Dycore::halo_exchange (Dycore.h:608-711): periodic x / y ghosts, wall ghosts in z, on the divided arrays

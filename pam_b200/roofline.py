@@ -9,9 +9,21 @@ and writes each of the N = 5+NT fields 8 times in total.
 
 _TV_TERMS = {2: 1, 3: 2, 4: 4, 5: 6, 7: 12, 9: 20}   # terms of coefs_to_tv for n coefficients (tools/gen_tables.py)
 
+# Instrumented count of one Dycore::reconstruct: the reference's algorithm, operation for operation, run on a scalar type
+# that counts its additions/subtractions, multiplications and divisions (tools/flopcount/count_flops.cpp over
+# pam_b200/cxx/Dycore.h reconstruct_generic; `python tools/count_flops.py`, output in profiles/r02_flop_count.json).
+# FROZEN: tests/test_host_logic.py re-counts and compares. order -> (add, mul, div)
+RECON_OPS = {3: (66, 67, 16), 5: (132, 141, 22), 7: (236, 261, 28), 9: (382, 429, 34)}
+
 
 def recon_flops(ord):
-    """(flops, of which divides) of one Dycore::reconstruct at order `ord`."""
+    """(flops, of which divides) of one Dycore::reconstruct at order `ord` (instrumented count; a divide counts as 1)."""
+    a, m, d = RECON_OPS[ord]
+    return a + m + d, d
+
+
+def recon_flops_hand_formula(ord):
+    """The hand count the instrumented one replaced (kept as a cross-check: within 2 % at every order)."""
     m = (ord + 1) // 2
     tv = lambda n: 3 * _TV_TERMS[n] - 1
     add = 0

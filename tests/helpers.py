@@ -40,20 +40,6 @@ def gpu_fields(c):
     return {n: dm.get(n, readonly=True).cpu().numpy() for n in names}
 
 
-def dycore_state_from_fields(o, fields):
-    """Conserved (rho, rho u, rho v, rho w, rho theta) + tracers from coupler fields, the way
-    Dycore::convert_coupler_to_dynamics does (Dycore.h:1370-1387); numpy, test-side only."""
-    R_d, R_v, C0, gamma = o.option("R_d"), o.option("R_v"), o.option("C0"), o.option("gamma_d")
-    names = o.tracer_names
-    rho_d, T = fields["density_dry"], fields["temp"]
-    rho_v = fields["water_vapor"]
-    press = rho_d * R_d * T + rho_v * R_v * T
-    rho = rho_d.copy()
-    for (n, pos, adds) in zip(names, [True] * len(names), [None] * len(names)):
-        pass
-    return R_d, R_v, C0, gamma, press, rho
-
-
 # ---------------------------------------------------------------------------------------------------------------------
 # Coupler modules either side of the dycore (SURVEY.md 8f): a numpy "DataManager" with the P3+SHOC tracer set and GCM
 # columns, shared by the oracle tests (CPU) and the CUDA parity tests.

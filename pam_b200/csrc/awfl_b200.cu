@@ -663,7 +663,7 @@ struct awfl_handle {
 // finds it taken by a different grid reads its own global-memory table instead (MatSel VT 3 / 2). Nothing is uploaded
 // or synchronised inside a time step, so handles on different host threads or devices never race on it.
 static thread_local std::string g_create_err;
-struct CvtabSlot { int refs = 0; std::vector<double> table; };
+struct CvtabSlot { int refs = 0; std::vector<double> table; std::vector<int> levels; };
 static std::mutex g_cvtab_mu;
 static std::map<std::pair<int, int>, CvtabSlot> g_cvtab;   // (device, ord) -> owner table
 
@@ -878,23 +878,24 @@ static int labits_for(const awfl_handle *h, int dir) {
 
 // Claim the constant-bank table of (device, order) for this handle (see g_cvtab). Called from awfl_create with the
 // handle's device current. Returns true when the handle may read c_vtab.
-static bool claim_cvtab(awfl_handle *h, const std::vector<double> &vtab) {
+static bool claim_cvtab(awfl_handle *h, const std::vector<double> &vtab, const std::vector<int> &levels) {
   std::lock_guard<std::mutex> lk(g_cvtab_mu);
   CvtabSlot &slot = g_cvtab[std::make_pair(h->cfg.device, h->ord)];
   if (slot.refs > 0) {
-    if (slot.table != vtab) return false;
+    if (slot.table != vtab || slot.levels != levels) return false;
     slot.refs++;
     return true;
   }
   int rc = 0;
   switch (h->ord) {
-    case 3: rc = OrdLaunch<3>::upload_cvtab(vtab.data(), vtab.size()); break;
-    case 5: rc = OrdLaunch<5>::upload_cvtab(vtab.data(), vtab.size()); break;
-    case 7: rc = OrdLaunch<7>::upload_cvtab(vtab.data(), vtab.size()); break;
-    default: rc = OrdLaunch<9>::upload_cvtab(vtab.data(), vtab.size()); break;
+    case 3: rc = OrdLaunch<3>::upload_cvtab(vtab.data(), vtab.size(), levels.data(), levels.size()); break;
+    case 5: rc = OrdLaunch<5>::upload_cvtab(vtab.data(), vtab.size(), levels.data(), levels.size()); break;
+    case 7: rc = OrdLaunch<7>::upload_cvtab(vtab.data(), vtab.size(), levels.data(), levels.size()); break;
+    default: rc = OrdLaunch<9>::upload_cvtab(vtab.data(), vtab.size(), levels.data(), levels.size()); break;
   }
   if (rc != 0) return false;
   slot.table = vtab;
+  slot.levels = levels;
   slot.refs = 1;
   return true;
 }
@@ -995,6 +996,7 @@ int awfl_create(const awfl_config *cfg, awfl_handle **out) {
   if ((long)cfg->nx * cfg->nens >= (1L << 31) || ((long)cfg->nx * cfg->nens + 255) / 256 * cfg->nz * cfg->ny >= (1L << 31)) {
     g_create_err = "awfl_create: nx*nens and the block count of one field must fit 31 bits"; return 1;
   }
+  if ((double)cfg->nz * cfg->ny * cfg->nx * cfg->nens >= 4294967296.0) { g_create_err = "awfl_create: one field must hold fewer than 2^32 cells (34 GB)"; return 1; }
   if (cfg->nx < hs0 || (cfg->ny > 1 && cfg->ny < hs0) || cfg->nz < hs0) { g_create_err = "awfl_create: each active dimension needs at least (ord+1)/2 cells"; return 1; }
   if (!cfg->dz_host) { g_create_err = "awfl_create: dz_host is NULL"; return 1; }
   if (cfg->num_tracers > 0 && (!cfg->tracer_positive || !cfg->tracer_adds_mass)) { g_create_err = "awfl_create: tracer flag arrays are NULL"; return 1; }
@@ -1050,7 +1052,21 @@ int awfl_create(const awfl_config *cfg, awfl_handle **out) {
     case 7: OrdLaunch<7>::configure(); break;
     default: OrdLaunch<9>::configure(); break;
   }
-  h->use_cvtab = h->shared_grid && vtab.size() <= OrdLaunch<5>::cvtab_capacity() && !getenv("AWFL_NO_CVTAB") && claim_cvtab(h, vtab);
+  if (h->shared_grid && !getenv("AWFL_NO_CVTAB")) {
+    // constant-bank copy: levels with bit-identical tables share one (an equally spaced grid has a single table at any order)
+    const size_t nel = (size_t)h->hs * h->hs * h->hs + (size_t)h->ord * h->ord;
+    std::vector<double> ctab;
+    std::vector<int> lvl(g.nz + 2);
+    for (int k = 0; k < g.nz + 2; k++) {
+      const double *tk = vtab.data() + (size_t)k * nel;
+      int found = -1;
+      for (size_t u = 0; u + nel <= ctab.size() && found < 0; u += nel)
+        if (memcmp(ctab.data() + u, tk, nel * sizeof(double)) == 0) found = (int)u;
+      if (found < 0) { found = (int)ctab.size(); ctab.insert(ctab.end(), tk, tk + nel); }
+      lvl[k] = found;
+    }
+    h->use_cvtab = ctab.size() <= OrdLaunch<5>::cvtab_capacity() && lvl.size() <= OrdLaunch<5>::cvtab_max_levels() && claim_cvtab(h, ctab, lvl);
+  }
   const size_t fb = sizeof(double) * (size_t)g.ncell;
   const size_t lvl = sizeof(double) * (size_t)g.ny * g.nx * g.nens;
 #define ALLOC(ptr, bytes) do { if (cudaMalloc((void **)&(ptr), (bytes)) != cudaSuccess) return bail(std::string("cudaMalloc failed for ") + #ptr); } while (0)
@@ -1300,7 +1316,7 @@ int awfl_time_step_host(awfl_handle *h, double *const *host_fields, double crm_d
   ENTER(h);
   NvtxRange nvtx_("awfl_time_step_host");
   if (!(crm_dt > 0.0)) return fail(h, "awfl_time_step_host: crm_dt must be positive");
-  // AWFL_HOST_TRACE=1: device timeline of this call on stderr (timing events on the three streams; diagnostic only)
+  // AWFL_HOST_TRACE=1: device timeline of this call on stderr (timing events on the streams; diagnostic only)
   static const bool trace = getenv("AWFL_HOST_TRACE") && atoi(getenv("AWFL_HOST_TRACE")) > 0;
   std::vector<std::pair<std::string, cudaEvent_t>> marks;
   auto mark = [&](const char *what, int s, cudaStream_t st) {
@@ -1322,7 +1338,8 @@ int awfl_time_step_host(awfl_handle *h, double *const *host_fields, double crm_d
     CK(cudaStreamCreateWithFlags(&h->s_out, cudaStreamNonBlocking));
     for (int c = 0; c < 4; c++) CK(cudaStreamCreateWithFlags(&h->s_cmp[c], cudaStreamNonBlocking));
   }
-  while ((int)h->slab_ev.size() < 2 * P + 3) {
+  // events per slab: 3s = inputs on the device, 3s+1 = converted (its CFL minimum is in), 3s+2 = results staged; 3P = start
+  while ((int)h->slab_ev.size() < 3 * P + 1) {
     cudaEvent_t e;
     CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     h->slab_ev.push_back(e);
@@ -1344,39 +1361,43 @@ int awfl_time_step_host(awfl_handle *h, double *const *host_fields, double crm_d
     const double inf = INFINITY;
     CK(cudaMemcpyAsync(h->dt_min_d, &inf, sizeof(double), cudaMemcpyHostToDevice, h->stream));
   }
-  // the copy streams must not run ahead of earlier work on the compute stream (staging buffers, tracer pointer tables,
-  // dt reset)
-  CK(cudaEventRecord(h->slab_ev[2 * P], h->stream));
-  CK(cudaStreamWaitEvent(h->s_in, h->slab_ev[2 * P], 0));
-  CK(cudaStreamWaitEvent(h->s_out, h->slab_ev[2 * P], 0));
+  // no stream may run ahead of earlier work on the handle's stream (staging buffers, tracer pointer tables, dt reset)
+  const int ev_start = 3 * P;
+  CK(cudaEventRecord(h->slab_ev[ev_start], h->stream));
+  CK(cudaStreamWaitEvent(h->s_in, h->slab_ev[ev_start], 0));
+  CK(cudaStreamWaitEvent(h->s_out, h->slab_ev[ev_start], 0));
   const bool alt = h->host_cstreams > 1 && P > 1;
   const int nc = h->host_cstreams > 4 ? 4 : h->host_cstreams;
-  if (alt) for (int c = 0; c < nc; c++) CK(cudaStreamWaitEvent(h->s_cmp[c], h->slab_ev[2 * P], 0));
+  if (alt) for (int c = 0; c < nc; c++) CK(cudaStreamWaitEvent(h->s_cmp[c], h->slab_ev[ev_start], 0));
   cudaStream_t const user_stream = h->stream;
   mark("start", 0, h->s_in);
   const int predicted = need_dt ? h->host_last_ncycles : ncycles_override;
   int qi = 0;   // buffer that holds the advanced state (the same for every slab: it depends on the sub-cycle count only)
   std::vector<Geom> slab(P, g);
   const size_t rows = (size_t)g.nz * g.ny * g.nx, pitch = sizeof(double) * (size_t)g.nens;
-  // the sub-cycles of slab s on its compute stream, after event `after` (the launch helpers enqueue on h->stream)
-  auto advance_slab = [&](int s, int n, double dts, int after) -> int {
-    h->stream = alt ? h->s_cmp[s % nc] : user_stream;
-    cudaError_t e = cudaStreamWaitEvent(h->stream, h->slab_ev[after], 0);
-    mark("advance_start", s, h->stream);
-    if (e == cudaSuccess) {
-      qi = step_advance(h, slab[s], n, dts);
-      mark("advanced", s, h->stream);
-      e = cudaEventRecord(h->slab_ev[2 * s + 1], h->stream);
-    }
-    h->stream = user_stream;
-    if (e != cudaSuccess) return fail(h, std::string("awfl_time_step_host: ") + cudaGetErrorString(e));
+  auto slab_stream = [&](int s) { return alt ? h->s_cmp[s % nc] : user_stream; };
+  // The two copy streams carry NOTHING but copies: the conversion kernels of a slab run on its compute stream. (They used to
+  // sit between the copies; on a GPU filled by three slabs of marching kernels a conversion waits for free block slots, and
+  // every such wait was a bubble on the host link -- the end-to-end step was bound by the device-to-host chain at 36 GB/s.)
+  // slab s: conversion in (+ CFL minimum) on its compute stream as soon as its inputs have arrived
+  auto convert_in_slab = [&](int s) -> int {
+    cudaStream_t cs = slab_stream(s);
+    CK(cudaStreamWaitEvent(cs, h->slab_ev[3 * s], 0));
+    step_convert_in(h, slab[s], fp, need_dt, cs);
+    CK(cudaEventRecord(h->slab_ev[3 * s + 1], cs));
     return 0;
   };
-  // results of slab s: conversion into the result staging + D2H, on the copy-out stream, after event 2s+1
-  auto results_out = [&](int s) -> int {
-    CK(cudaStreamWaitEvent(h->s_out, h->slab_ev[2 * s + 1], 0));
-    step_convert_out(h, slab[s], fpo, qi, h->s_out);
-    mark("converted_out", s, h->s_out);
+  // slab s: its sub-cycles and the conversion into the RESULT staging on its compute stream, then the copies out
+  auto advance_slab = [&](int s, int n, double dts) -> int {
+    cudaStream_t cs = slab_stream(s);
+    h->stream = cs;                                   // the launch helpers enqueue on h->stream
+    mark("advance_start", s, cs);
+    qi = step_advance(h, slab[s], n, dts);
+    h->stream = user_stream;
+    mark("advanced", s, cs);
+    step_convert_out(h, slab[s], fpo, qi, cs);
+    CK(cudaEventRecord(h->slab_ev[3 * s + 2], cs));
+    CK(cudaStreamWaitEvent(h->s_out, h->slab_ev[3 * s + 2], 0));
     for (int v = 0; v < N; v++) {
       if (P == 1) CK(cudaMemcpyAsync(host_fields[v], h->stage_out + (size_t)v * g.ncell, fb, cudaMemcpyDeviceToHost, h->s_out));
       else CK(cudaMemcpy2DAsync(host_fields[v] + slab[s].e0, pitch, h->stage_out + (size_t)v * g.ncell + slab[s].e0, pitch,
@@ -1394,16 +1415,17 @@ int awfl_time_step_host(awfl_handle *h, double *const *host_fields, double crm_d
       else CK(cudaMemcpy2DAsync(h->stage_fields + (size_t)v * g.ncell + slab[s].e0, pitch, host_fields[v] + slab[s].e0, pitch,
                                 sizeof(double) * (size_t)slab[s].ne, rows, cudaMemcpyHostToDevice, h->s_in));
     }
+    CK(cudaEventRecord(h->slab_ev[3 * s], h->s_in));
     mark("h2d_done", s, h->s_in);
-    step_convert_in(h, slab[s], fp, need_dt, h->s_in);
-    CK(cudaEventRecord(h->slab_ev[2 * s], h->s_in));
-    if (predicted > 0) {
-      if (advance_slab(s, predicted, crm_dt / predicted, 2 * s)) return 1;
-      if (results_out(s)) return 1;
-    }
+    if (convert_in_slab(s)) return 1;
+    if (predicted > 0 && advance_slab(s, predicted, crm_dt / predicted)) return 1;
   }
   int ncycles = ncycles_override;
-  if (need_dt && step_ncycles(h, crm_dt, &ncycles, h->s_in)) return 1;
+  if (need_dt) {
+    // the CFL minimum is complete when every slab has been converted
+    for (int s = 0; s < P; s++) CK(cudaStreamWaitEvent(h->s_in, h->slab_ev[3 * s + 1], 0));
+    if (step_ncycles(h, crm_dt, &ncycles, h->s_in)) return 1;
+  }
   h->host_last_ncycles = ncycles;
   const double dt = crm_dt / ncycles;       // Dycore.h:145
   if (predicted > 0 && predicted != ncycles) {
@@ -1411,21 +1433,21 @@ int awfl_time_step_host(awfl_handle *h, double *const *host_fields, double crm_d
     // un-overlapped; its results overwrite the speculative ones in the host buffers
     h->host_mispredictions++;
     CK(cudaStreamSynchronize(h->s_out));
+    if (alt) for (int c = 0; c < nc; c++) CK(cudaStreamSynchronize(h->s_cmp[c]));
     step_convert_in(h, g, fp, false);
     qi = step_advance(h, g, ncycles, dt);
     step_convert_out(h, g, fpo, qi);
-    CK(cudaEventRecord(h->slab_ev[1], h->stream));
-    CK(cudaStreamWaitEvent(h->s_out, h->slab_ev[1], 0));
+    CK(cudaEventRecord(h->slab_ev[ev_start], h->stream));
+    CK(cudaStreamWaitEvent(h->s_out, h->slab_ev[ev_start], 0));
     for (int v = 0; v < N; v++) CK(cudaMemcpyAsync(host_fields[v], h->stage_out + (size_t)v * g.ncell, fb, cudaMemcpyDeviceToHost, h->s_out));
   } else if (predicted <= 0) {
-    for (int s = 0; s < P; s++) {
-      if (advance_slab(s, ncycles, dt, 2 * (P - 1))) return 1;      // the dt needed every slab's conversion
-      if (results_out(s)) return 1;
-    }
+    for (int s = 0; s < P; s++)
+      if (advance_slab(s, ncycles, dt)) return 1;      // the dt needed every slab's conversion: all of them are done by now
   }
   CK(cudaGetLastError());
   CK(cudaStreamSynchronize(h->s_out));
   if (alt) for (int c = 0; c < nc; c++) CK(cudaStreamSynchronize(h->s_cmp[c]));
+  CK(cudaStreamSynchronize(h->s_in));
   CK(cudaStreamSynchronize(h->stream));
   if (trace) {
     for (size_t m = 1; m < marks.size(); m++) {

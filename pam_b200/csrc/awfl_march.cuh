@@ -60,8 +60,12 @@ template <int ORD> struct MarchCfg {
   static constexpr size_t SMEM_TRACER = (size_t)(2 * (ORD + 3)) * MT * sizeof(double);   // two lines per warp
 };
 
-// x^g for x > 0 (normal range): exp(g*log(x)). Relative error <~ 3e-15 for the arguments met here (|g log x| < 20),
+// x^g for x > 0 (normal range): exp(g*log(x)). Relative error <~ 4e-15 for the arguments met here (|g log x| < 40),
 // against 94 FP64-pipe instructions for the correctly rounded pow(): 49. Stated in DESIGN.md (tolerance budget).
+// (CUDA's exp and log carry their coefficients as immediates -- two UMOV each, a fifth of the x march's non-FP64
+// instructions. A hand-written pair with constant-bank coefficients removed those UMOVs and was SLOWER, inlined (spills) or
+// called, plain or Estrin-form polynomial: x march 5.96 -> 6.33 ... 7.68 ms, profiles/r02i_pow_variants.txt,
+// r02j_pow_variants.txt. The library pair's dependency chains are shorter; the UMOVs ride the uniform datapath.)
 __device__ __forceinline__ double pow_pos(double x, double g) { return exp(g * log(x)); }
 
 struct Raw { double r, ru, rv, rw, rt, p; };
@@ -120,6 +124,18 @@ __device__ __forceinline__ EOn<NV> weno_ring_inl(const double *fb, int head, M m
   return r;
 }
 
+// Slow path of the tracer march: one reconstruction with the overflow-proof weights (weno_EO_n<.., SAFE = true>), taken
+// when the fast form returned a non-finite value. Never inlined: it must not cost the fast path a register.
+template <int ORD, class M>
+__device__ __noinline__ EOn<1> weno_ring_safe(const double *fb, int head, M m) {
+  double u[1][ORD];
+#pragma unroll
+  for (int s = 0; s < ORD; s++) u[0][s] = fb[ring_slot<ORD>(head, s)];
+  EOn<1> r;
+  weno_EO_n<ORD, 1, M, true>(u, m, r.E, r.O);
+  return r;
+}
+
 // Matrix provider of a step: VT 0 = constant horizontal tables, 1 = vertical tables in the constant bank (all members
 // share one vertical grid), 2 = vertical tables in global memory with a run-time element stride (member-dependent grid),
 // 3 = in global memory with unit stride (shared grid whose table is too large for the constant bank).
@@ -130,7 +146,7 @@ template <int ORD> struct MatSel<ORD, 0> {
 };
 template <int ORD> struct MatSel<ORD, 1> {
   using type = CMat<ORD>;
-  static __device__ __forceinline__ type get(const double *, long, long, int level) { type m; m.base = level * CMat<ORD>::NEL; return m; }
+  static __device__ __forceinline__ type get(const double *, long, long, int level) { type m; m.base = c_vlvl[level]; return m; }
 };
 template <int ORD> struct MatSel<ORD, 2> {
   using type = VMat<ORD>;
@@ -180,25 +196,39 @@ k_march_state(const Geom g, const Phys ph, const SweepArgs a) {
   if (!decode_item<DIR>(g, a.sbits, a.labits, it)) return;
   const int n = DIR == 0 ? g.nx : (DIR == 1 ? g.ny : g.nz);
   const long sd = stride_of(DIR, g);
-  const long nc = g.ncell;
+  // cells of one field: fits 32 bits (checked by awfl_create), which lets a field offset k * nc be ONE 32 x 32 -> 64 bit
+  // multiply-add instead of a 64-bit product
+  const size_t nc = (unsigned)g.ncell;
   const double *__restrict__ q = a.qin;
   double *const rb = ring_smem + threadIdx.x;            // this thread's column: entry e at rb[e*MT]
   double *const fpv = rb + (RF_COUNT * ORD) * MT;        // previous interface: fluxes [0..4], right-edge values [5..8]
   double *const stg = fpv + (NS + 4) * MT;               // staged read-modify-write operands of the current group
   const long voff = a.vst > 1 ? it.e : 0;
 
-  auto fetch = [&](int c) -> Raw {
-    int cw;
-    if (DIR == 2) cw = c < 0 ? 0 : (c >= n ? n - 1 : c);            // wall ghosts derive from the boundary cell
-    else cw = c < 0 ? c + n : (c >= n ? c - n : c);                 // periodic, Dycore.h:629-657
-    const long idx = it.base + (long)cw * sd;
+  // Cells are fetched in marching order through a cursor that moves one cell per fetch -- across the periodic seam in the
+  // horizontal marches, clamped at the walls in the vertical one (wall ghosts derive from the boundary cell) -- instead of
+  // a 64-bit index product per cell and field.
+  auto wrapped = [&](int c) -> int {
+    if (DIR == 2) return c < 0 ? 0 : (c >= n ? n - 1 : c);
+    return c < 0 ? c + n : (c >= n ? c - n : c);                      // periodic, Dycore.h:629-657
+  };
+  int fc = it.c0 - 1 - (HS - 1);                                      // next cell to fetch (unwrapped)
+  const long seam_back = (long)(n - 1) * sd;
+  const double *qp = q + it.base + (long)wrapped(fc) * sd;
+  const long pdelta = a.pcache - q;                                   // the pressure of a cell sits at the same offset in its own field
+  auto fetch_next = [&]() -> Raw {
     Raw x;
-    x.r = __ldg(q + idx); x.ru = __ldg(q + nc + idx); x.rv = __ldg(q + 2 * nc + idx); x.rw = __ldg(q + 3 * nc + idx);
-    x.rt = __ldg(q + 4 * nc + idx);
+    x.r = __ldg(qp); x.ru = __ldg(qp + nc); x.rv = __ldg(qp + 2 * nc); x.rw = __ldg(qp + 3 * nc);
+    x.rt = __ldg(qp + 4 * nc);
     // the pressure C0 (rho theta)^gamma of a cell is the same in every direction of a stage: the x march (always the
     // first sweep) computes it, the other marches read it back -- one x^gamma (~160 instructions) per cell and stage
     // instead of one per direction
-    x.p = DIR == 0 ? 0.0 : __ldg(a.pcache + idx);
+    x.p = DIR == 0 ? 0.0 : __ldg(qp + pdelta);
+    long step;
+    if (DIR == 2) step = (fc >= 0 && fc < n - 1) ? sd : 0;            // clamped at the walls
+    else step = wrapped(fc) == n - 1 ? -seam_back : sd;               // back across the seam
+    qp += step;
+    fc++;
     return x;
   };
   // conserved -> primitives + pressure (Dycore.h:310-321); wall ghosts per Dycore.h:662-710 with the intended
@@ -240,12 +270,12 @@ k_march_state(const Geom g, const Phys ph, const SweepArgs a) {
   const double rdd_h = DIR == 0 ? 1.0 / g.dx : 1.0 / g.dy;
   double mL = 0.0, pL = 0.0, mRs = 0.0, mLns = 0.0;
   const int jfirst = it.c0 - 1 - (HS - 1), jlast = it.c1 + HS - 1;
-  Raw cur = fetch(jfirst);
+  Raw cur = fetch_next();
 
 #pragma unroll 1
   for (int j = jfirst; j <= jlast; j++) {
     Raw nxt = cur;
-    if (j < jlast) nxt = fetch(j + 1);
+    if (j < jlast) nxt = fetch_next();
     const int c = j - (HS - 1);        // cell whose window c-HS+1..c+HS-1 will be complete after this put
     const bool upd_on = c > it.c0;             // cell c-1 has both interfaces
     const int cc = c - 1;
@@ -274,13 +304,18 @@ k_march_state(const Geom g, const Phys ph, const SweepArgs a) {
     // z march's stall samples, 7.31 -> 7.12 ms)
     constexpr bool PRE_ALL = V0_UNROLL > 1;
     const bool ld_t = upd_on && !a.first, ld_q = upd_on && MODE == 1 && a.a != 0.0;
+    // Cursors over the five state variables l = 0..4 of cell c-1, advanced once per variable. (Addressed as base + l * stride
+    // with the run-time l of the rolled vertical march, every access cost 8-9 integer instructions -- the 64-bit l * ncell
+    // and the shared-memory slots: a quarter of the z march's non-FP64 instructions, profiles/r02d_state_z_line_mix.txt.)
+    const double *pf_t = a.tend + idx, *pf_q = a.qbase + idx;   // operands still to be staged: partial tendency, step-start state
+    double *pf_s = stg;                                        // ... and where they are staged: (tend, base) pairs
     auto start_copies = [&](int g0) {
 #pragma unroll
       for (int i = 0; i < NV; i++) {
-        const int v = g0 + i;
-        if (v > 0) {
-          if (ld_t) cp_async8(stg + (2 * (v - 1)) * MT, a.tend + (v - 1) * nc + idx);
-          if (ld_q) cp_async8(stg + (2 * (v - 1) + 1) * MT, a.qbase + (v - 1) * nc + idx);   // qout may alias qbase: read before the write below
+        if (g0 + i > 0) {
+          if (ld_t) cp_async8(pf_s, pf_t);
+          if (ld_q) cp_async8(pf_s + MT, pf_q);   // qout may alias qbase: read before the write below
+          pf_s += 2 * MT; pf_t += nc; pf_q += nc;
         }
       }
     };
@@ -289,6 +324,11 @@ k_march_state(const Geom g, const Phys ph, const SweepArgs a) {
       for (int g0 = 0; g0 < 6; g0 += NV) { start_copies(g0); cp_async_commit(); }
     }
     if (!PRE_ALL && (ld_t || ld_q)) { start_copies(0); cp_async_commit(); }
+    double *po = (MODE == 0 ? a.tend : a.qout) + idx;           // where variable l of cell c-1 goes
+    const double *sg = stg;                                     // its staged operands
+    double *fl = fpv;                                           // flux of variable l through the previous interface
+    double *fe = fpv + (NS - 1) * MT;                           // right-edge value of variable l (l >= 1) in the previous cell
+    const double *rl = rb + ((RF_U - 1) * ORD) * MT + so;       // primitive variable l (l >= 1) of cell c-1 in the ring
     // reconstructed quantities in ring order: rho*u_n, p (acoustic pair), then u, v, w, theta -- NV at a time
 #pragma unroll(V0_UNROLL)
     for (int v0 = 0; v0 < 6; v0 += NV) {
@@ -309,6 +349,10 @@ k_march_state(const Geom g, const Phys ph, const SweepArgs a) {
         const int v = v0 + i;
         const double E = eo.E[i], O = eo.O[i];
         if (v == 0) { mRs = E - O; mLns = E + O; continue; }
+        // this variable's cursors; the shared ones move on to the next variable
+        double *const po_l = po, *const fl_l = fl, *const fe_l = fe;
+        const double *const sg_l = sg, *const rl_l = rl;
+        po += nc; sg += 2 * MT; fl += MT; fe += MT; rl += ORD * MT;
         int l;
         double F;
         if (v == 1) {
@@ -327,28 +371,28 @@ k_march_state(const Geom g, const Phys ph, const SweepArgs a) {
           l = idR; F = rn;
         } else {
           l = v - 1;                   // idU..idT
-          F = rn * (up ? fpv[(NS + v - 2) * MT] : E - O);
-          fpv[(NS + v - 2) * MT] = E + O;
+          F = rn * (up ? fe_l[0] : E - O);
+          fe_l[0] = E + O;
           if (l == NORMAL) F += pp;
         }
         if (!flux_on) continue;
         if (upd_on) {
-          const double div = (F - fpv[l * MT]) * rdd;
-          double T = (ld_t ? stg[(2 * (v - 1)) * MT] : 0.0) - div;
-          if (MODE == 0) a.tend[l * nc + idx] = T;
+          const double div = (F - fl_l[0]) * rdd;
+          double T = (ld_t ? sg_l[0] : 0.0) - div;
+          if (MODE == 0) po_l[0] = T;
           else {
             if (l == idW) T = fma(-gv, rho, T);                 // Dycore.h:560
             if (l == idV && g.sim2d) T = 0.0;                   // Dycore.h:565
-            if (MODE == 2) a.qout[l * nc + idx] = T;
+            if (MODE == 2) po_l[0] = T;
             else {
               // round-tripped stage input (x/rho)*rho, Dycore.h:316-319 + :527-530
-              const double rt = l == idR ? rho : rb[((RF_U + l - 1) * ORD) * MT + so] * rho;
-              const double o = fma(a.a, ld_q ? stg[(2 * (v - 1) + 1) * MT] : 0.0, a.b * rt);
-              a.qout[l * nc + idx] = fma(a.c, T, o);
+              const double rt = l == idR ? rho : rl_l[0] * rho;
+              const double o = fma(a.a, ld_q ? sg_l[MT] : 0.0, a.b * rt);
+              po_l[0] = fma(a.c, T, o);
             }
           }
         }
-        fpv[l * MT] = F;
+        fl_l[0] = F;
       }
     }
   }
@@ -372,7 +416,7 @@ k_march_tracer(const Geom g, const TracerSweepArgs a) {
   if (tr >= g.nt) return;
   const int n = DIR == 0 ? g.nx : (DIR == 1 ? g.ny : g.nz);
   const long sd = stride_of(DIR, g);
-  const long nc = g.ncell;
+  const size_t nc = (unsigned)g.ncell;                        // < 2^32, see k_march_state
   const double *__restrict__ rho = a.qin;
   const double *__restrict__ tq = a.qin + (long)(NS + tr) * nc;
   double *__restrict__ fl = a.tflux + (long)tr * (DIR == 2 ? nc + nc / g.nz : nc);
@@ -415,6 +459,15 @@ k_march_tracer(const Geom g, const TracerSweepArgs a) {
     const typename MatSel<ORD, VT>::type mat = MatSel<ORD, VT>::get(a.vtab, a.vst, voff, c + 1);
     EOn<NL> eo;
     if constexpr (VT == 0) eo = weno_ring<ORD, NL>(rb, head, mat); else eo = weno_ring_inl<ORD, NL>(rb, head, mat);
+    // tracers carry arbitrary units (number concentrations ...): a magnitude that overflows the fast weights gives NaN or
+    // inf -- one test for both lines (a sum that overflows by itself only sends finite values through the slow path too)
+    if (!(fabs(eo.E[0]) + fabs(eo.E[1]) <= 1.7976931348623157e308)) {
+#pragma unroll
+      for (int v = 0; v < NL; v++) {
+        const EOn<1> sf = weno_ring_safe<ORD>(rb + (v * ORD) * MT, head, mat);
+        eo.E[v] = sf.E[0]; eo.O[v] = sf.O[0];
+      }
+    }
 #pragma unroll
     for (int v = 0; v < NL; v++) {
       const double E = eo.E[v], O = eo.O[v];

@@ -79,13 +79,17 @@ void OrdLaunch<ORD>::configure() {
 }
 
 template <int ORD>
-int OrdLaunch<ORD>::upload_cvtab(const double *host, size_t ndoubles) {
-  if (ndoubles > (size_t)AWFL_CVTAB_DOUBLES) return (int)cudaErrorInvalidValue;
-  return (int)cudaMemcpyToSymbol(c_vtab, host, ndoubles * sizeof(double), 0, cudaMemcpyHostToDevice);
+int OrdLaunch<ORD>::upload_cvtab(const double *host, size_t ndoubles, const int *level_offsets, size_t nlevels) {
+  if (ndoubles > (size_t)AWFL_CVTAB_DOUBLES || nlevels > (size_t)AWFL_CVLVL_MAX) return (int)cudaErrorInvalidValue;
+  cudaError_t e = cudaMemcpyToSymbol(c_vtab, host, ndoubles * sizeof(double), 0, cudaMemcpyHostToDevice);
+  if (e == cudaSuccess) e = cudaMemcpyToSymbol(c_vlvl, level_offsets, nlevels * sizeof(int), 0, cudaMemcpyHostToDevice);
+  return (int)e;
 }
 
 template <int ORD>
 size_t OrdLaunch<ORD>::cvtab_capacity() { return (size_t)AWFL_CVTAB_DOUBLES; }
+template <int ORD>
+size_t OrdLaunch<ORD>::cvtab_max_levels() { return (size_t)AWFL_CVLVL_MAX; }
 
 template <int ORD>
 void OrdLaunch<ORD>::hydro_pint(cudaStream_t s, const Geom &g, const Phys &ph, const HydroArgs &a, bool shared) {

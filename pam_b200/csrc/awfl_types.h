@@ -64,8 +64,9 @@ template <int ORD> struct OrdLaunch {
   static void march_state(cudaStream_t s, const Geom &g, const Phys &ph, const SweepArgs &a, int dir, int mode, int vt);
   static void march_tracer(cudaStream_t s, const Geom &g, const TracerSweepArgs &a, int dir, int vt);
   static void configure();   // per-device kernel attributes (shared-memory rings) of every marching kernel of this order
-  static int upload_cvtab(const double *host, size_t ndoubles);   // synchronous; returns a cudaError_t
+  static int upload_cvtab(const double *host, size_t ndoubles, const int *level_offsets, size_t nlevels);   // synchronous; returns a cudaError_t
   static size_t cvtab_capacity();
+  static size_t cvtab_max_levels();
   static void hydro_pint(cudaStream_t s, const Geom &g, const Phys &ph, const HydroArgs &a, bool shared);
   static void reconstruct(cudaStream_t s, const double *st, int n, int ind, int level, int iens, int nens, const double *vtab, bool shared, double *out);
 };

@@ -140,10 +140,16 @@ template <int ORD> struct UMat {
 // Vertical matrices of a grid shared by all ensemble members, held in the constant bank: the level index is uniform
 // across a warp of the marching kernels, so every element is one constant-cache load (no vector-memory traffic).
 // Same per-level layout as VMat. Uploaded by OrdLaunch<ORD>::upload_cvtab.
+// Levels whose tables are bit-identical share one copy (on an equally spaced grid that is every level, and then even the
+// 206-double ord-9 table of 60 levels fits): c_vlvl[level] is the offset of the level's table in c_vtab.
 #ifndef AWFL_CVTAB_DOUBLES
-#define AWFL_CVTAB_DOUBLES 7424
+#define AWFL_CVTAB_DOUBLES 7168
+#endif
+#ifndef AWFL_CVLVL_MAX
+#define AWFL_CVLVL_MAX 512
 #endif
 static __constant__ double c_vtab[AWFL_CVTAB_DOUBLES];
+static __constant__ int c_vlvl[AWFL_CVLVL_MAX];
 template <int ORD> struct CMat {
   static constexpr bool is_const = false;
   static constexpr int HS = (ORD + 1) / 2;
@@ -193,7 +199,13 @@ template <class M> __device__ __forceinline__ bool nonzero_hi(const M &m, int r,
 // (O) parts at the cell edges: value(left edge, x=-1/2) = E - O ; value(right edge, x=+1/2) = E + O. The NV
 // reconstructions are independent; evaluating them together shares every table load between them (one uniform load per
 // NV FP64 instructions) and gives the FP64 pipe NV independent dependency chains.
-template <int ORD, int NV, class M>
+//
+// SAFE = true evaluates the weights the way the reference writes them -- every weight divided on its own, no products of
+// the (tv^2 + eps) factors -- which stays finite for data of any magnitude. The fast form multiplies hs+1 factors of order
+// data^4 and overflows FP64 beyond |data| ~ 1e19 (ord 5) / 7e12 (ord 9); it then returns NaN (never a wrong finite value:
+// any overflowing product poisons the common denominator), which the tracer march tests for and redoes with SAFE = true.
+// The state march reconstructs rho*u, p, u, v, w, theta, whose physical magnitudes (<= 1e6) are far from that range.
+template <int ORD, int NV, class M, bool SAFE = false>
 __device__ __forceinline__ void weno_EO_n(const double (&u)[NV][ORD], const M &m, double (&E)[NV], double (&O)[NV]) {
   constexpr int HS = (ORD + 1) / 2;
   constexpr int N = HS + 1;
@@ -272,6 +284,24 @@ __device__ __forceinline__ void weno_EO_n(const double (&u)[NV][ORD], const M &m
     for (int i = 0; i < HS; i++) tl[i] = tv[v][i];
     const double avg = tree_sum<HS>(tl) * C::rhs();
     tv[v][HS] = fma(tv[v][HS] - avg, C::sigma(), avg);
+    if constexpr (SAFE) {
+      double w[N], sum = 0.0;
+#pragma unroll
+      for (int i = 0; i < N; i++) { w[i] = C::idl(i) / fma(tv[v][i], tv[v][i], eps); sum += w[i]; }
+      double sum2 = 0.0;
+#pragma unroll
+      for (int i = 0; i < N; i++) {
+        const double d = C::idl(i), x = w[i] / (sum + eps);
+        w[i] = x * (d + d * d - 3.0 * d * x + x * x) / (d * d + x * (1.0 - 2.0 * d));
+        sum2 += w[i];
+      }
+      double Eb = 0.0, Ob = 0.0;
+#pragma unroll
+      for (int i = 0; i < N; i++) { const double x = w[i] / (sum2 + eps); Eb = fma(x, e[v][i], Eb); Ob = fma(x, o2[v][i], Ob); }
+      E[v] = Eb;
+      O[v] = 0.5 * Ob;
+      continue;
+    }
     // Weights (WenoLimiter.h:142-166): w_i = idl_i/(tv_i^2+eps); convexify; map_weights; convexify. Both normalisations
     // are carried out over a common denominator -- w_i/(sum_j w_j + eps) = idl_i P_i / (sum_j idl_j P_j + eps P) with
     // P_i = prod_{j!=i}(tv_j^2+eps), P = prod_j(tv_j^2+eps) -- the same rational expression evaluated with two

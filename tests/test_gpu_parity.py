@@ -412,3 +412,25 @@ def test_two_devices_in_one_process_and_parity_of_each_shard():
             assert rel_l2(got[k], r, fl[k]) <= TOL_STEP, (rank, k)
         d.finalize()
     assert torch.cuda.current_device() == 0
+
+
+@pytest.mark.parametrize("ord", [5, 9])
+def test_tracers_of_huge_magnitude_take_the_overflow_proof_weights(ord):
+    """The fast WENO weights share a denominator that is a product of hs+1 factors of order data^4: beyond |q/rho| ~ 7e12
+    (ord 9) / 1e19 (ord 5) it overflows FP64. A tracer may carry any unit (number concentrations per kg ...), so the
+    tracer march redoes such a reconstruction with the reference's per-weight divisions. Two number tracers scaled to
+    1e15 / 1e21 per kg must still match the oracle."""
+    case = _case(nz=12, nx=12, nens=33, nt=10)
+    f = case["fields"]
+    f["cloud_water_num"] = np.ascontiguousarray(f["cloud_water_num"] * 1e15 + 1e14)
+    f["ice_num"] = np.ascontiguousarray(f["ice_num"] * 1e21 + 1e20)
+    o = H.make_oracle(case, ord, crm_dt=2.0)
+    c, d = H.make_gpu(case, ord, crm_dt=2.0)
+    o.declare_hydrostatic()
+    d.declare_current_profile_as_hydrostatic(c)
+    assert o.time_step() == d.timeStep(c)
+    ref, got = o.get_fields(), H.gpu_fields(c)
+    fl = field_floors(ref)
+    for k in ref:
+        assert np.isfinite(got[k]).all(), k
+        assert rel_l2(got[k], ref[k], fl[k]) <= TOL_STEP, (k, rel_l2(got[k], ref[k], fl[k]))

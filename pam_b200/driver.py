@@ -44,7 +44,10 @@ def vertical_interfaces(config):
     if vc == "uniform":
         if "crm_nz" not in config:
             endrun("To use uniform vertical grid you need to specify crm_nz")
-        nz, zlen = int(config["crm_nz"]), float(config["zlen"])
+        nz, zlen = int(config["crm_nz"]), float(config.get("zlen", -1))            # driver.cpp:101: as<real>(-1)
+        if zlen <= 0:
+            endrun("ERROR: a uniform vertical grid needs zlen (with the AWFL dycore the reference's set_domain_sizes is a no-op, "
+                   "pamc_init.h:43-53, and zlen stays -1)")
         dz = zlen / (nz - 1)                                   # driver.cpp:156 (sic: nz-1, first and last cells are half cells)
         z = np.array([0.0 if k == 0 else (zlen if k == nz else k * dz - dz / 2) for k in range(nz + 1)])
         return z
@@ -119,7 +122,9 @@ def run(config_path, device="cuda:0", ord=5, quiet=False):
     out_freq = float(config["out_freq"])
     out_prefix = str(config["out_prefix"])
     if xlen <= 0 or ylen <= 0:
-        endrun("ERROR: xlen and ylen must be given")
+        # driver.cpp:130-133 asks set_domain_sizes for missing lengths, which only the PAM-C dycore answers (pamc_init.h:43-53:
+        # the body sits under #ifdef PAMC_DYCORE); with AWFL the reference goes on with xlen = -1. Stop instead.
+        endrun("ERROR: xlen and ylen must be given (the AWFL build of the reference has no default domain size)")
     nsteps_gcm = int(math.ceil(sim_time / dt_gcm))                       # driver.cpp:120-123
     dt_gcm = sim_time / nsteps_gcm
     nsteps_crm_phys = int(math.ceil(dt_gcm / dt_crm_phys))
@@ -144,7 +149,12 @@ def run(config_path, device="cuda:0", ord=5, quiet=False):
         print("Vertical interface heights: " + "  ".join("%g" % z for z in zint) + "\n")
     if not idealized:
         initialize_from_supercell_column(zint, coupler)
-    dycore.declare_current_profile_as_hydrostatic(coupler)
+    # The reference's standalone driver never calls declare_current_profile_as_hydrostatic, so its AWFL run integrates with
+    # whatever the pool block behind "variable_gravity" last held. Here the initial profile is declared
+    # hydrostatic once, like the MMF driver does; `b200_declare_hydrostatic: false` in the YAML file reproduces the
+    # reference's call sequence exactly (variable_gravity then stays 0).
+    if bool(config.get("b200_declare_hydrostatic", True)):
+        dycore.declare_current_profile_as_hydrostatic(coupler)
 
     out = Output(coupler, out_prefix)
     etime_gcm, num_out, steps = 0.0, 0, 0

@@ -34,3 +34,36 @@ for name, kw, ord in CASES:
             out.append("step %d: worst %.2e (%s)" % (step, worst[0], worst[1]))
     print("%-24s %s" % (name, "; ".join(out)), flush=True)
     d.finalize()
+
+# ---- against the reference's OWN kernels on this GPU (oracle/_ref/libpam_ref_ord5_cuda.so: the unmodified reference through
+# its YAKL CUDA backend): its step with the bottom-ghost race neutralised ("intended", the oracle's semantics) and its
+# unmodified Dycore::timeStep ("raw": whatever the racing threads and the pool's stale memory give) ----
+from oracle import pamcuda
+if pamcuda.available("ref", 5):
+    print("\nagainst the reference's YAKL-CUDA build on the same GPU (one step, worst field):")
+    for name, kw, ord in [c for c in CASES if c[2] == 5]:
+        case = syn.make_case(**kw)
+        c, d = H.make_gpu(case, ord, crm_dt=2.0)
+        d.declare_current_profile_as_hydrostatic(c)
+        gv = c.get_data_manager_device_readonly().get("variable_gravity").cpu().numpy()
+        res = {}
+        for mode in ("intended", "raw"):
+            r = pamcuda.PamCudaDycore("ref", case["nz"], case["ny"], case["nx"], case["nens"], case["xlen"], case["ylen"], case["zint"],
+                                      tracers=case["tracers"], consts=case["consts"], crm_dt=2.0, ord=ord)
+            r.set_fields(case["fields"])
+            r.set_field("variable_gravity", gv)
+            if mode == "intended":
+                r.time_step_public()
+            else:
+                r.time_step()
+            res[mode] = r.get_fields()
+            r.close()
+        d.timeStep(c)
+        got = H.gpu_fields(c)
+        fl = field_floors(res["intended"])
+        w_int = max((rel_l2(got[k], res["intended"][k], fl[k]), k) for k in got)
+        w_raw = max((rel_l2(got[k], res["raw"][k], fl[k]), k) for k in got)
+        w_rr = max((rel_l2(res["raw"][k], res["intended"][k], fl[k]), k) for k in got)
+        print("%-24s this repo vs intended %.2e (%s); vs raw timeStep %.2e (%s); reference raw vs its own intended %.2e (%s)"
+              % (name, w_int[0], w_int[1], w_raw[0], w_raw[1], w_rr[0], w_rr[1]), flush=True)
+        d.finalize()

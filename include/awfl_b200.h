@@ -183,6 +183,10 @@ int awfl_reconstruct(awfl_handle *h, const double *stencils, int n, int ind, int
  * 2 = a member-strided global table (member-dependent grid). Results do not depend on it (same arithmetic). */
 int awfl_table_home(const awfl_handle *h);
 
+/* Debug aid: fills every scratch buffer of the handle with NaN bit patterns (on the handle's stream). A later call that
+ * read scratch memory before writing it returns NaN -- the check compute-sanitizer's initcheck would make. */
+int awfl_poison_workspace(awfl_handle *h);
+
 /* Number of kernel launches issued by this handle since creation (bench.py reports the per-step count). */
 long awfl_launch_count(const awfl_handle *h);
 

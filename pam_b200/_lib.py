@@ -36,7 +36,7 @@ EXPORTS = ("awfl_create", "awfl_destroy", "awfl_last_error", "awfl_dycore_name",
            "awfl_profile_end", "awfl_set_variable_gravity", "awfl_export_tables", "awfl_copy_to_host", "awfl_copy_to_device",
            "awfl_current_device", "awfl_device_alloc", "awfl_device_free", "awfl_set_host_slabs", "awfl_host_slabs", "awfl_host_mispredictions", "awfl_init_idealized",
            "awfl_table_home", "awfl_convert_coupler_to_dynamics", "awfl_convert_dynamics_to_coupler", "awfl_halo_exchange",
-           "awfl_compute_tendencies_haloed", "awfl_compute_mass_dynamics", "awfl_init_supercell")
+           "awfl_compute_tendencies_haloed", "awfl_compute_mass_dynamics", "awfl_init_supercell", "awfl_poison_workspace")
 
 KERNEL_CLASSES = ("in", "out", "state_x", "state_y", "state_z", "tracer_x", "tracer_y", "tracer_z", "fct", "tracer_upd", "other")
 
@@ -85,6 +85,7 @@ def load():
     lib.awfl_host_mispredictions.argtypes = [C.c_void_p]
     lib.awfl_host_mispredictions.restype = C.c_long
     lib.awfl_table_home.argtypes = [C.c_void_p]
+    lib.awfl_poison_workspace.argtypes = [C.c_void_p]
     lib.awfl_convert_coupler_to_dynamics.argtypes = [C.c_void_p, C.POINTER(AwflFields), C.c_void_p, C.c_void_p]
     lib.awfl_convert_dynamics_to_coupler.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(AwflFields)]
     lib.awfl_halo_exchange.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]

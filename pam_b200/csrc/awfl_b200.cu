@@ -1461,6 +1461,29 @@ int awfl_time_step_host(awfl_handle *h, double *const *host_fields, double crm_d
   return 0;
 }
 
+// Debug aid (compute-sanitizer's initcheck is not available on every pool): every scratch buffer of the handle -- the two
+// stage states, partial tendencies, mass and tracer fluxes, FCT multipliers, the pressure cache, the host path's staging --
+// is filled with NaN bit patterns. A step that read any of them before writing it would return NaN.
+int awfl_poison_workspace(awfl_handle *h) {
+  ENTER(h);
+  const Geom &g = h->g;
+  const size_t fb = sizeof(double) * (size_t)g.ncell, lvl = sizeof(double) * (size_t)g.ny * g.nx * g.nens;
+  const int N = NS + g.nt;
+  for (int b = 0; b < 3; b++) CK(cudaMemsetAsync(h->Q[b], 0xff, fb * N, h->stream));
+  CK(cudaMemsetAsync(h->tend, 0xff, fb * NS, h->stream));
+  CK(cudaMemsetAsync(h->pcache, 0xff, fb, h->stream));
+  for (int d = 0; d < 3; d++) {
+    CK(cudaMemsetAsync(h->mflux[d], 0xff, d == 2 ? fb + lvl : fb, h->stream));
+    CK(cudaMemsetAsync(h->tflux[d], 0xff, (d == 2 ? fb + lvl : fb) * g.nt, h->stream));
+  }
+  CK(cudaMemsetAsync(h->mult, 0xff, fb * g.nt, h->stream));
+  CK(cudaMemsetAsync(h->pint, 0xff, fb + lvl, h->stream));
+  if (h->stage_fields) CK(cudaMemsetAsync(h->stage_fields, 0xff, fb * N, h->stream));
+  if (h->stage_out) CK(cudaMemsetAsync(h->stage_out, 0xff, fb * N, h->stream));
+  if (h->halo_pressure) CK(cudaMemsetAsync(h->halo_pressure, 0xff, sizeof(double) * (size_t)halo_dims(g, h->hs).nh, h->stream));
+  return 0;
+}
+
 long awfl_host_mispredictions(const awfl_handle *h) { return h->host_mispredictions; }
 
 int awfl_compute_tendencies(awfl_handle *h, const double *state, const double *tracers, const double *fct_start, double dt,

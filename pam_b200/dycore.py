@@ -238,6 +238,10 @@ class Dycore:
         """Slab count the next time_step_host will use (0 passed to set_host_slabs = chosen from the grid)."""
         return int(self.lib.awfl_host_slabs(self.h))
 
+    def poison_workspace(self):
+        """Debug aid: NaN-fill every scratch buffer of the handle (a step that reads scratch before writing it shows NaN)."""
+        self._rc(self.lib.awfl_poison_workspace(self.h), "awfl_poison_workspace")
+
     def table_home(self):
         """1: vertical matrices in the constant bank, 3: unit-stride global table, 2: member-strided global table."""
         return int(self.lib.awfl_table_home(self.h))

@@ -434,3 +434,50 @@ def test_tracers_of_huge_magnitude_take_the_overflow_proof_weights(ord):
     for k in ref:
         assert np.isfinite(got[k]).all(), k
         assert rel_l2(got[k], ref[k], fl[k]) <= TOL_STEP, (k, rel_l2(got[k], ref[k], fl[k]))
+
+
+@pytest.mark.parametrize("cfg", [dict(), dict(ny=5, nx=6, nz=8, nens=33), dict(nt=10, nens=32), dict(nt=10, ny=5, nx=6, nz=8, nens=8),
+                                 dict(per_ens=True), dict(ord=9, nz=12)])
+def test_scratch_memory_is_never_read_before_it_is_written_and_steps_repeat_bit_for_bit(cfg):
+    """What compute-sanitizer's initcheck / racecheck would look for, done by hand (the tool is closed on this GPU pool):
+    (1) every scratch buffer of the handle is NaN-poisoned before a step, through the device-resident and the host-buffer
+    entry points and declare_hydrostatic -- the results must be the bits of an unpoisoned run (a read of stale scratch
+    would show NaN or differ); (2) the same step from the same inputs three times gives identical bits (an unsynchronised
+    shared-memory ring, cp.async staging read too early, or an aliasing stage buffer would show up as run-to-run
+    differences at these sizes, where several segments, tiles and ragged lanes are in flight at once)."""
+    import torch
+    cfg = dict(cfg)
+    ord = cfg.pop("ord", 5)
+    case = _case(**cfg)
+    runs = []
+    for poison in (False, True, True):
+        c, d = H.make_gpu(case, ord, crm_dt=2.0)
+        names = list(H.STATE_FIELDS) + c.get_tracer_names()
+        host = [np.ascontiguousarray(case["fields"][n]).copy() for n in names]
+        if poison:
+            d.time_step_host(host, 2.0, ncycles=1)          # allocates the staging buffers, so that they get poisoned too
+            host = [np.ascontiguousarray(case["fields"][n]).copy() for n in names]
+            d.poison_workspace()
+        d.declare_current_profile_as_hydrostatic(c)
+        if poison:
+            d.poison_workspace()
+        n1 = d.timeStep(c)
+        if poison:
+            d.poison_workspace()
+        n2 = d.timeStep(c)
+        if poison:
+            d.poison_workspace()
+        d.set_host_slabs(2)
+        d.time_step_host(host, 2.0); d.time_step_host(host, 2.0)
+        torch.cuda.synchronize()
+        runs.append((n1, n2, H.gpu_fields(c), host))
+        d.finalize()
+    for r in runs[1:]:
+        assert r[:2] == runs[0][:2]
+        for k in runs[0][2]:
+            assert np.isfinite(r[2][k]).all(), k
+            assert np.array_equal(r[2][k], runs[0][2][k]), k
+        for a, b in zip(r[3], runs[0][3]):
+            assert np.array_equal(a, b)
+    for k, a in zip(list(H.STATE_FIELDS) + [t[0] for t in case["tracers"]], runs[0][3]):
+        assert np.array_equal(a, runs[0][2][k]), k       # host path == resident path

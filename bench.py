@@ -460,7 +460,10 @@ def main():
                                 "reference algorithm has flops (row-form WENO, shared denominators), so `frac` (algorithmic) reads higher"}
     except Exception:
         pass
-    dur = dom_ms / max(dom_n, 1) * 1e-3
+    # one "launch" of a class = its work of one Runge-Kutta stage (a vertical march that runs page by page -- ord 9 with a
+    # paged table -- is several kernel launches per stage: their times add up)
+    stage_launches = r["prof_steps"] * cyc[-1] * 3
+    dur = dom_ms / max(stage_launches if dom not in ("in", "out") else dom_n, 1) * 1e-3
     roof = {"bound": "fp64", "kernel": dom, "achieved": fl / dur / 1e12, "peak": fp64_peak, "unit": "TFLOP/s",
             "frac": fl / dur / 1e12 / fp64_peak, "traffic": traffic, "executed": executed,
             "peak_source": "DFMA-chain microbenchmark run in this process (awfl_measure_fp64_peak); FP64 peak is not in MEASURED_PEAKS.json",

@@ -180,7 +180,9 @@ int awfl_reconstruct(awfl_handle *h, const double *stencils, int n, int ind, int
 /* Where the z marches of this handle read their per-level vertical matrices: 1 = the constant bank of (device, ord),
  * claimed at awfl_create and shared by handles whose tables are bit-identical; 3 = a global-memory table with unit
  * stride (shared vertical grid, but the constant bank is held by a handle with another grid, or the table does not fit);
- * 2 = a member-strided global table (member-dependent grid). Results do not depend on it (same arithmetic). */
+ * 2 = a member-strided global table (member-dependent grid); 4 = the constant bank used page by page (a shared grid whose
+ * table does not fit as a whole, e.g. ord 9 at 58 levels: the z marches run segment by segment behind the upload of the
+ * levels each segment reads; needs the bank for itself). Results do not depend on it (same arithmetic). */
 int awfl_table_home(const awfl_handle *h);
 
 /* Debug aid: fills every scratch buffer of the handle with NaN bit patterns (on the handle's stream). A later call that

@@ -629,6 +629,13 @@ struct awfl_handle {
   double *mult;          // nt fields
   double *dz, *rdz, *grav_var, *vtab, *vs2c, *vwrl, *pint;
   bool use_cvtab;               // shared vertical grid whose table fits the constant bank
+  // ... or does not fit, but the levels ONE SEGMENT of the vertical marches needs do: the z marches then run segment by
+  // segment, each launch preceded by the upload of its page (pinned host copy -> constant bank, on the launching stream)
+  bool use_cvpage;
+  bool cvpage_ok;               // false while the host-buffer entry point runs slabs on several streams (they would overwrite each other's pages)
+  int cvpage_sbits;             // 2^sbits segments = pages per line
+  double *vtab_pin;             // pinned host copy of the whole kernel table
+  int *vlvl_pin;                // pinned: per page, level -> offset in the page
   double *dt_min_d, *dt_min_h;   // device scalar + pinned host scalar
   double *mass_d;
   unsigned char *positive_d, *adds_mass_d;
@@ -663,7 +670,7 @@ struct awfl_handle {
 // finds it taken by a different grid reads its own global-memory table instead (MatSel VT 3 / 2). Nothing is uploaded
 // or synchronised inside a time step, so handles on different host threads or devices never race on it.
 static thread_local std::string g_create_err;
-struct CvtabSlot { int refs = 0; std::vector<double> table; std::vector<int> levels; };
+struct CvtabSlot { int refs = 0; bool exclusive = false; std::vector<double> table; std::vector<int> levels; };
 static std::mutex g_cvtab_mu;
 static std::map<std::pair<int, int>, CvtabSlot> g_cvtab;   // (device, ord) -> owner table
 
@@ -882,7 +889,7 @@ static bool claim_cvtab(awfl_handle *h, const std::vector<double> &vtab, const s
   std::lock_guard<std::mutex> lk(g_cvtab_mu);
   CvtabSlot &slot = g_cvtab[std::make_pair(h->cfg.device, h->ord)];
   if (slot.refs > 0) {
-    if (slot.table != vtab || slot.levels != levels) return false;
+    if (slot.exclusive || slot.table != vtab || slot.levels != levels) return false;
     slot.refs++;
     return true;
   }
@@ -899,8 +906,16 @@ static bool claim_cvtab(awfl_handle *h, const std::vector<double> &vtab, const s
   slot.refs = 1;
   return true;
 }
+// Paged use rewrites the bank inside every step: the handle must be its only user.
+static bool claim_cvtab_exclusive(awfl_handle *h) {
+  std::lock_guard<std::mutex> lk(g_cvtab_mu);
+  CvtabSlot &slot = g_cvtab[std::make_pair(h->cfg.device, h->ord)];
+  if (slot.refs > 0) return false;
+  slot.refs = 1; slot.exclusive = true; slot.table.clear(); slot.levels.clear();
+  return true;
+}
 static void release_cvtab(awfl_handle *h) {
-  if (!h->use_cvtab) return;
+  if (!h->use_cvtab && !h->use_cvpage) return;
   std::lock_guard<std::mutex> lk(g_cvtab_mu);
   auto it = g_cvtab.find(std::make_pair(h->cfg.device, h->ord));
   if (it != g_cvtab.end() && --it->second.refs <= 0) {
@@ -908,18 +923,48 @@ static void release_cvtab(awfl_handle *h) {
     cudaDeviceSynchronize();
     g_cvtab.erase(it);
   }
-  h->use_cvtab = false;
+  h->use_cvtab = false; h->use_cvpage = false;
 }
 
+// home of the vertical matrices a z march reads: 1 constant bank (whole table, or the current page), 3 / 2 global memory
+static int vtable_home(const awfl_handle *h, int mode, bool tracer) {
+  if (h->use_cvtab || (h->use_cvpage && h->cvpage_ok)) return 1;
+  return h->shared_grid && (tracer || mode == 1) ? 3 : 2;
+}
 static void launch_state_sweep(awfl_handle *h, const Geom &g, int dir, int mode, const SweepArgs &a) {
   ProfScope ps(h, KC_STATE_X + dir);
-  AWFL_ORD_DISPATCH(march_state(h->stream, g, h->ph, a, dir, mode, dir == 2 ? (h->use_cvtab ? 1 : (h->shared_grid && mode == 1 ? 3 : 2)) : 0));
+  AWFL_ORD_DISPATCH(march_state(h->stream, g, h->ph, a, dir, mode, dir == 2 ? vtable_home(h, mode, false) : 0));
 }
 
 static void launch_tracer_sweep(awfl_handle *h, const Geom &g, int dir, TracerSweepArgs a) {
   if (g.nt == 0) return;
-  ProfScope ps(h, KC_TRACER_X + dir);
-  AWFL_ORD_DISPATCH(march_tracer(h->stream, g, a, dir, dir == 2 ? (h->use_cvtab ? 1 : (h->shared_grid ? 3 : 2)) : 0));
+  // the grid carries (tracer, line index, segment) in blockIdx.z, which CUDA limits to 65535: tall grids with many tracers
+  // (nz = 128, nx >= 768: 2048 work items per tracer) go in chunks of tracers
+  int per_launch = 65535 >> (a.labits + a.sbits);
+  if (per_launch < 1) per_launch = 1;
+  for (int t0 = 0; t0 < g.nt; t0 += per_launch) {
+    a.tr0 = t0; a.ntr = g.nt - t0 < per_launch ? g.nt - t0 : per_launch;
+    ProfScope ps(h, KC_TRACER_X + dir);
+    AWFL_ORD_DISPATCH(march_tracer(h->stream, g, a, dir, dir == 2 ? vtable_home(h, 1, true) : 0));
+  }
+}
+
+// Page p of the vertical table: the levels segment p of the z marches reads (cells c0-1 .. c1 -> levels c0 .. c1+1).
+static int upload_cvpage(awfl_handle *h, int p) {
+  const int n = h->g.nz, sb = h->cvpage_sbits;
+  const int c0 = (p * n) >> sb, c1 = ((p + 1) * n) >> sb;
+  const size_t nel = (size_t)h->hs * h->hs * h->hs + (size_t)h->ord * h->ord;
+  const double *src = h->vtab_pin + (size_t)c0 * nel;
+  const size_t cnt = (size_t)(c1 + 2 - c0) * nel;
+  const int *lv = h->vlvl_pin + (size_t)p * (n + 2);
+  int rc = 0;
+  switch (h->ord) {
+    case 3: rc = OrdLaunch<3>::upload_cvpage(h->stream, src, cnt, lv, n + 2); break;
+    case 5: rc = OrdLaunch<5>::upload_cvpage(h->stream, src, cnt, lv, n + 2); break;
+    case 7: rc = OrdLaunch<7>::upload_cvpage(h->stream, src, cnt, lv, n + 2); break;
+    default: rc = OrdLaunch<9>::upload_cvpage(h->stream, src, cnt, lv, n + 2); break;
+  }
+  return rc;
 }
 
 // One semi-discrete right-hand side + stage combination.
@@ -937,9 +982,23 @@ static void run_stage(awfl_handle *h, const Geom &g, const double *qin, const do
     s.qin = qin; s.qbase = q0; s.qout = mode == 2 ? st_out : qout; s.tend = h->tend; s.mflux = h->mflux[dir];
     s.dz = h->dz; s.grav_var = h->grav_var; s.vtab = h->vtab; s.rdz = h->rdz; s.pcache = h->pcache; s.vst = h->shared_grid ? 1 : g.nens;
     s.a = a; s.b = b; s.c = b * dt_full; s.first = d == 0; s.sbits = sbits_state(h, g, dir, nn[dir]); s.labits = labits_for(h, dir);
-    launch_state_sweep(h, g, dir, last ? mode : 0, s);
+    s.seg_only = -1;
     TracerSweepArgs t;
     t.qin = qin; t.mflux = h->mflux[dir]; t.tflux = h->tflux[dir]; t.vtab = h->vtab; t.vst = s.vst; t.sbits = sbits_for(h, nn[dir]); t.labits = s.labits;
+    t.seg_only = -1;
+    if (dir == 2 && h->use_cvpage && h->cvpage_ok) {
+      // paged vertical table: segment by segment, the state and the tracer march of a page behind its upload (stream order
+      // keeps a page in place until the launches that read it are done)
+      s.sbits = t.sbits = h->cvpage_sbits;
+      for (int p = 0; p < (1 << h->cvpage_sbits); p++) {
+        if (upload_cvpage(h, p) != 0) { h->err = "upload of a vertical-table page failed"; return; }
+        s.seg_only = t.seg_only = p;
+        launch_state_sweep(h, g, dir, last ? mode : 0, s);
+        launch_tracer_sweep(h, g, dir, t);
+      }
+      continue;
+    }
+    launch_state_sweep(h, g, dir, last ? mode : 0, s);
     launch_tracer_sweep(h, g, dir, t);
   }
   if (g.nt > 0 && g.sim2d && mode == 1 && !fct_start && h->fused_fct) {
@@ -986,7 +1045,7 @@ const char *awfl_last_error(const awfl_handle *h) { return h ? h->err.c_str() : 
 
 long awfl_launch_count(const awfl_handle *h) { return h->launches; }
 
-int awfl_table_home(const awfl_handle *h) { return h->use_cvtab ? 1 : (h->shared_grid ? 3 : 2); }
+int awfl_table_home(const awfl_handle *h) { return h->use_cvtab ? 1 : (h->use_cvpage ? 4 : (h->shared_grid ? 3 : 2)); }
 
 int awfl_create(const awfl_config *cfg, awfl_handle **out) {
   *out = nullptr;
@@ -997,6 +1056,11 @@ int awfl_create(const awfl_config *cfg, awfl_handle **out) {
     g_create_err = "awfl_create: nx*nens and the block count of one field must fit 31 bits"; return 1;
   }
   if ((double)cfg->nz * cfg->ny * cfg->nx * cfg->nens >= 4294967296.0) { g_create_err = "awfl_create: one field must hold fewer than 2^32 cells (34 GB)"; return 1; }
+  {
+    int lab = 0;
+    while ((1 << lab) < (cfg->nz > cfg->ny ? cfg->nz : cfg->ny)) lab++;
+    if ((1L << (lab + 4)) > 65535) { g_create_err = "awfl_create: nz and ny must not exceed 2048 (line index + segment bits of a march must fit gridDim.z)"; return 1; }
+  }
   if (cfg->nx < hs0 || (cfg->ny > 1 && cfg->ny < hs0) || cfg->nz < hs0) { g_create_err = "awfl_create: each active dimension needs at least (ord+1)/2 cells"; return 1; }
   if (!cfg->dz_host) { g_create_err = "awfl_create: dz_host is NULL"; return 1; }
   if (cfg->num_tracers > 0 && (!cfg->tracer_positive || !cfg->tracer_adds_mass)) { g_create_err = "awfl_create: tracer flag arrays are NULL"; return 1; }
@@ -1005,6 +1069,7 @@ int awfl_create(const awfl_config *cfg, awfl_handle **out) {
   awfl_handle *h = new awfl_handle();
   h->cfg = *cfg;
   h->launches = 0;
+  h->use_cvpage = false; h->cvpage_ok = false; h->cvpage_sbits = 0; h->vtab_pin = nullptr; h->vlvl_pin = nullptr;
   h->prof = false; h->ev_used = 0;
   h->ord = cfg->ord; h->hs = hs0;
   Geom &g = h->g;
@@ -1066,6 +1131,29 @@ int awfl_create(const awfl_config *cfg, awfl_handle **out) {
       lvl[k] = found;
     }
     h->use_cvtab = ctab.size() <= OrdLaunch<5>::cvtab_capacity() && lvl.size() <= OrdLaunch<5>::cvtab_max_levels() && claim_cvtab(h, ctab, lvl);
+    if (!h->use_cvtab && !getenv("AWFL_NO_CVPAGE") && lvl.size() <= OrdLaunch<5>::cvtab_max_levels()) {
+      // too large as a whole (ord 9 at 58 levels: 60 x 206 doubles = 97 KB): page it by segments of the vertical marches
+      int sb = 1;
+      auto fits = [&](int b) {
+        for (int p = 0; p < (1 << b); p++) {
+          const int c0 = (p * g.nz) >> b, c1 = ((p + 1) * g.nz) >> b;
+          if ((size_t)(c1 + 2 - c0) * nel > OrdLaunch<5>::cvtab_capacity()) return false;
+        }
+        return true;
+      };
+      while (sb < 4 && !fits(sb)) sb++;
+      if (fits(sb) && (g.nz >> sb) >= 4 && claim_cvtab_exclusive(h)) {
+        h->use_cvpage = true; h->cvpage_ok = true; h->cvpage_sbits = sb;
+        const int P = 1 << sb;
+        if (cudaMallocHost((void **)&h->vtab_pin, sizeof(double) * vtab.size()) != cudaSuccess ||
+            cudaMallocHost((void **)&h->vlvl_pin, sizeof(int) * (size_t)P * (g.nz + 2)) != cudaSuccess) return bail("cudaMallocHost failed");
+        memcpy(h->vtab_pin, vtab.data(), sizeof(double) * vtab.size());
+        for (int p = 0; p < P; p++) {
+          const int c0 = (p * g.nz) >> sb, c1 = ((p + 1) * g.nz) >> sb;
+          for (int k = 0; k < g.nz + 2; k++) h->vlvl_pin[(size_t)p * (g.nz + 2) + k] = (k >= c0 && k <= c1 + 1) ? (int)((k - c0) * nel) : 0;
+        }
+      }
+    }
   }
   const size_t fb = sizeof(double) * (size_t)g.ncell;
   const size_t lvl = sizeof(double) * (size_t)g.ny * g.nx * g.nens;
@@ -1129,6 +1217,8 @@ void awfl_destroy(awfl_handle *h) {
   if (h->s_in) { cudaStreamDestroy(h->s_in); cudaStreamDestroy(h->s_out); for (int c = 0; c < 4; c++) cudaStreamDestroy(h->s_cmp[c]); }
   for (cudaEvent_t e : h->slab_ev) cudaEventDestroy(e);
   if (h->dt_min_h) cudaFreeHost(h->dt_min_h);
+  if (h->vtab_pin) cudaFreeHost(h->vtab_pin);
+  if (h->vlvl_pin) cudaFreeHost(h->vlvl_pin);
   for (cudaEvent_t e : h->ev_pool) cudaEventDestroy(e);
   if (h->own_stream && h->stream) cudaStreamDestroy(h->stream);
   delete h;
@@ -1369,6 +1459,12 @@ int awfl_time_step_host(awfl_handle *h, double *const *host_fields, double crm_d
   const bool alt = h->host_cstreams > 1 && P > 1;
   const int nc = h->host_cstreams > 4 ? 4 : h->host_cstreams;
   if (alt) for (int c = 0; c < nc; c++) CK(cudaStreamWaitEvent(h->s_cmp[c], h->slab_ev[ev_start], 0));
+  // slabs on several streams would overwrite each other's pages of a paged vertical table: they read the global copy
+  struct PageGuard {
+    awfl_handle *h; bool saved;
+    PageGuard(awfl_handle *h_, bool off) : h(h_), saved(h_->cvpage_ok) { if (off) h->cvpage_ok = false; }
+    ~PageGuard() { h->cvpage_ok = saved; }
+  } page_guard(h, alt);
   cudaStream_t const user_stream = h->stream;
   mark("start", 0, h->s_in);
   const int predicted = need_dt ? h->host_last_ncycles : ncycles_override;

@@ -188,12 +188,15 @@ k_march_state(const Geom g, const Phys ph, const SweepArgs a) {
   constexpr double rcs = 1.0 / 350.0;
   constexpr int NORMAL = DIR == 0 ? idU : (DIR == 1 ? idV : idW);
   constexpr int NV = (DIR != 2 && ORD <= 5) ? AWFL_NV_H : AWFL_NV;             // reconstructions per group
-  constexpr int V0_UNROLL = DIR == 2 ? AWFL_V0_UNROLL_Z : AWFL_V0_UNROLL_H;   // unrolling of the loop over variable groups
+  // unrolling of the loop over variable groups. The vertical march stays rolled at ord >= 5 (unrolled, the copies share their
+  // per-level table loads and spill 0.8 / 1.6 KB at ord 5 / 7); ord 3 has 17 table values per level and unrolls without
+  // spills: z march 4.64 -> 4.14 ms on C4 (profiles/r02q_ord3_variants.txt)
+  constexpr int V0_UNROLL = DIR == 2 ? (ORD == 3 ? 3 : AWFL_V0_UNROLL_Z) : AWFL_V0_UNROLL_H;
   extern __shared__ double ring_smem[];
   Item it;
   // one warp per block: the march position depends on blockIdx only, so the compiler keeps the loop control and the
   // per-level matrix addresses in uniform registers
-  if (!decode_item<DIR>(g, a.sbits, a.labits, it)) return;
+  if (!decode_item<DIR>(g, a.sbits, a.labits, it, DIR == 2 ? a.seg_only : -1)) return;
   const int n = DIR == 0 ? g.nx : (DIR == 1 ? g.ny : g.nz);
   const long sd = stride_of(DIR, g);
   // cells of one field: fits 32 bits (checked by awfl_create), which lets a field offset k * nc be ONE 32 x 32 -> 64 bit
@@ -411,9 +414,9 @@ k_march_tracer(const Geom g, const TracerSweepArgs a) {
   Item it;                                                    // one warp per block (see k_march_state)
   // the two lines of a warp are adjacent levels k, k+1 for the horizontal marches and adjacent columns i, i+1 for the
   // vertical march (an odd count repeats the last line: the same values are written twice)
-  if (!decode_item<DIR, DIR == 2 ? 1 : NL, DIR == 2 ? NL : 1>(g, a.sbits, a.labits, it)) return;
-  const int tr = it.tr;
-  if (tr >= g.nt) return;
+  if (!decode_item<DIR, DIR == 2 ? 1 : NL, DIR == 2 ? NL : 1>(g, a.sbits, a.labits, it, DIR == 2 ? a.seg_only : -1)) return;
+  const int tr = a.tr0 + it.tr;
+  if (it.tr >= a.ntr || tr >= g.nt) return;
   const int n = DIR == 0 ? g.nx : (DIR == 1 ? g.ny : g.nz);
   const long sd = stride_of(DIR, g);
   const size_t nc = (unsigned)g.ncell;                        // < 2^32, see k_march_state

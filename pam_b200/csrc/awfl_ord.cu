@@ -52,7 +52,7 @@ void OrdLaunch<ORD>::march_state(cudaStream_t s, const Geom &g, const Phys &ph, 
 
 template <int ORD>
 void OrdLaunch<ORD>::march_tracer(cudaStream_t s, const Geom &g, const TracerSweepArgs &a, int dir, int vt) {
-  const dim3 blocks = march_grid(g, dir, a.sbits, a.labits, g.nt, 2);
+  const dim3 blocks = march_grid(g, dir, a.sbits, a.labits, a.ntr, 2);
   constexpr size_t B = MarchCfg<ORD>::SMEM_TRACER;
   if (dir == 0) AWFL_LAUNCH_MARCH((k_march_tracer<ORD, 0, 0>), B, g, a);
   else if (dir == 1) AWFL_LAUNCH_MARCH((k_march_tracer<ORD, 1, 0>), B, g, a);
@@ -83,6 +83,14 @@ int OrdLaunch<ORD>::upload_cvtab(const double *host, size_t ndoubles, const int 
   if (ndoubles > (size_t)AWFL_CVTAB_DOUBLES || nlevels > (size_t)AWFL_CVLVL_MAX) return (int)cudaErrorInvalidValue;
   cudaError_t e = cudaMemcpyToSymbol(c_vtab, host, ndoubles * sizeof(double), 0, cudaMemcpyHostToDevice);
   if (e == cudaSuccess) e = cudaMemcpyToSymbol(c_vlvl, level_offsets, nlevels * sizeof(int), 0, cudaMemcpyHostToDevice);
+  return (int)e;
+}
+
+template <int ORD>
+int OrdLaunch<ORD>::upload_cvpage(cudaStream_t s, const double *host_pinned, size_t ndoubles, const int *level_offsets_pinned, size_t nlevels) {
+  if (ndoubles > (size_t)AWFL_CVTAB_DOUBLES || nlevels > (size_t)AWFL_CVLVL_MAX) return (int)cudaErrorInvalidValue;
+  cudaError_t e = cudaMemcpyToSymbolAsync(c_vtab, host_pinned, ndoubles * sizeof(double), 0, cudaMemcpyHostToDevice, s);
+  if (e == cudaSuccess) e = cudaMemcpyToSymbolAsync(c_vlvl, level_offsets_pinned, nlevels * sizeof(int), 0, cudaMemcpyHostToDevice, s);
   return (int)e;
 }
 

@@ -61,11 +61,12 @@ struct Item {
 // LA_LINES / LB_LINES: lines per work item along the first / second line index (the tracer march takes two adjacent
 // lines per warp); it.la / it.lb are then the indices of the item's FIRST line.
 template <int DIR, int LA_LINES = 1, int LB_LINES = 1>
-__device__ __forceinline__ bool decode_item(const Geom &g, int sbits, int labits, Item &it) {
+__device__ __forceinline__ bool decode_item(const Geom &g, int sbits, int labits, Item &it, int seg_only = -1) {
   const int n = DIR == 0 ? g.nx : (DIR == 1 ? g.ny : g.nz);
   const int la_count = DIR == 2 ? g.ny : g.nz;
   const unsigned z = blockIdx.z;
   const int seg = (int)(z & ((1u << sbits) - 1u));
+  if (seg_only >= 0 && seg != seg_only) return false;      // block-uniform: the launch works on one page of levels
   it.la = (int)((z >> sbits) & ((1u << labits) - 1u)) * LA_LINES;
   it.tr = (int)(z >> (sbits + labits));
   it.lb = (int)blockIdx.y * LB_LINES;

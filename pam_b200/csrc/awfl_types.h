@@ -37,6 +37,7 @@ struct SweepArgs {
   double a, b, c;         // SSPRK3 stage coefficients (c = b*dt)
   int first;              // 1: this is the first sweep of the stage (tend is written, not accumulated)
   int sbits, labits;      // grid encoding (decode_item): 2^sbits segments per line, labits bits for the first line index
+  int seg_only;           // >= 0: only this segment of every line works, the other blocks leave at once (paged vertical tables)
 };
 
 // Tracer march arguments (k_march_tracer)
@@ -47,6 +48,8 @@ struct TracerSweepArgs {
   const double *vtab;
   long vst;             // element stride of vtab: nens or 1
   int sbits, labits;    // grid encoding (decode_item)
+  int seg_only;         // see SweepArgs
+  int tr0, ntr;         // tracers [tr0, tr0 + ntr) of this launch (gridDim.z = ntr << (labits + sbits) must stay <= 65535)
 };
 
 // declare_current_profile_as_hydrostatic arguments
@@ -65,6 +68,8 @@ template <int ORD> struct OrdLaunch {
   static void march_tracer(cudaStream_t s, const Geom &g, const TracerSweepArgs &a, int dir, int vt);
   static void configure();   // per-device kernel attributes (shared-memory rings) of every marching kernel of this order
   static int upload_cvtab(const double *host, size_t ndoubles, const int *level_offsets, size_t nlevels);   // synchronous; returns a cudaError_t
+  // one PAGE of the table (the levels a segment of the vertical marches needs), asynchronously on the launching stream
+  static int upload_cvpage(cudaStream_t s, const double *host_pinned, size_t ndoubles, const int *level_offsets_pinned, size_t nlevels);
   static size_t cvtab_capacity();
   static size_t cvtab_max_levels();
   static void hydro_pint(cudaStream_t s, const Geom &g, const Phys &ph, const HydroArgs &a, bool shared);

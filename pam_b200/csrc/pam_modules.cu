@@ -4,9 +4,10 @@
 //
 // Layout: ensemble member fastest, so one warp = 32 consecutive members of one (level[, field]) column set and every
 // global access is a coalesced 256-byte line. All of these modules reduce over the horizontal (j,i) of one level and
-// member: a thread owns one (level, member) column and walks its ny*nx cells in (j,i) order, which is the summation
-// order of the reference's serial backend (its GPU backend uses atomicAdd, i.e. no defined order). They are
-// HBM-bound streaming kernels; there is NO CPU fallback.
+// member: a block is 32 members x S segments of the column's ny*nx cells, each thread walks its run of cells in (j,i)
+// order and the S partial sums are combined in segment order (seg_combine): deterministic, no atomics -- the reference's
+// GPU backend uses atomicAdd, i.e. no defined order. With S = 1 (2-D CRMs) this is the summation order of the
+// reference's serial backend. They are HBM-bound streaming kernels; there is NO CPU fallback.
 #include <cuda_runtime.h>
 #include <math.h>
 #include <string>
@@ -40,30 +41,69 @@ namespace {
 
 struct Dims { int nz, ny, nx, nens; };
 
+// Work decomposition of the reducing kernels. A block is 32 consecutive members x S horizontal segments (threadIdx.x =
+// member lane: coalesced; threadIdx.y = segment): a thread walks a contiguous run of the ny*nx cells of its (level, member)
+// column in (j,i) order, the S partial sums of a column are combined in segment order by every thread of the column
+// (deterministic, no atomics). S = 1 (2-D CRMs: a column has 64 cells) is the summation order of the reference's serial
+// backend, bit for bit; a 3-D CRM (1024 cells per column, and perhaps only 128 members per GPU) gets S = 16, i.e. 16 x the
+// threads -- with one thread per column the C3 shard ran these kernels at 3-4 % of the HBM rate.
+constexpr int SEG_MAX = 16;
+static int seg_count(int nh) {
+  int s = nh / 64;
+  return s < 1 ? 1 : (s > SEG_MAX ? SEG_MAX : s);
+}
+struct SegItem { int e, c0, c1; bool active; };
+__device__ __forceinline__ SegItem seg_item(const Dims &d) {
+  SegItem it;
+  const int e = blockIdx.x * 32 + threadIdx.x, nh = d.ny * d.nx, S = blockDim.y, sg = threadIdx.y;
+  it.active = e < d.nens;
+  it.e = it.active ? e : d.nens - 1;       // lanes past the last member shadow it (they take part in the barriers, write nothing)
+  it.c0 = (int)((long)nh * sg / S);
+  it.c1 = (int)((long)nh * (sg + 1) / S);
+  return it;
+}
+// v[0..NV) -> the sums over the S segments of this lane's column, in segment order, in every thread of the column
+template <int NV>
+__device__ __forceinline__ void seg_combine(double (&v)[NV], double *sm) {
+  const int S = blockDim.y;
+  if (S == 1) return;
+  __syncthreads();                            // sm may still be read from a previous combine
+#pragma unroll
+  for (int q = 0; q < NV; q++) sm[(q * SEG_MAX + threadIdx.y) * 32 + threadIdx.x] = v[q];
+  __syncthreads();
+#pragma unroll
+  for (int q = 0; q < NV; q++) {
+    double t = sm[(q * SEG_MAX) * 32 + threadIdx.x];
+    for (int sg = 1; sg < S; sg++) t += sm[(q * SEG_MAX + sg) * 32 + threadIdx.x];
+    v[q] = t;
+  }
+}
+
 // ---------------------------------------------------------------------------------------------------------------
 // modules::sponge_layer (sponge_layer.h:9-96). One thread = (field, sponge level, member): horizontal mean in (j,i)
 // order (:71-74; zero for the w field, :32), then the relaxation of every cell of that level (:86-92).
 // ---------------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(128) k_sponge(const Dims d, double *const *fields, int num_fields, int num_layers,
-                                                const double *zint, const double *zmid, double time_factor) {
-  const int e = blockIdx.x * blockDim.x + threadIdx.x;
-  const int kloc = blockIdx.y, ifld = blockIdx.z;
-  if (e >= d.nens) return;
+__global__ void __launch_bounds__(32 * SEG_MAX) k_sponge(const Dims d, double *const *fields, int num_fields, int num_layers,
+                                                         const double *zint, const double *zmid, double time_factor) {
+  __shared__ double sm[SEG_MAX * 32];
+  const SegItem it = seg_item(d);
+  const int e = it.e, kloc = blockIdx.y, ifld = blockIdx.z;
   const int k = d.nz - 1 - kloc;
   double *f = fields[ifld] + (long)k * d.ny * d.nx * d.nens + e;
-  const int nh = d.ny * d.nx;
   const double r_nx_ny = 1.0 / (d.nx * d.ny);
-  double havg = 0.0;
+  double havg[1] = {0.0};
   if (ifld != 3) {
-    for (int c = 0; c < nh; c++) havg += f[(long)c * d.nens] * r_nx_ny;
+    for (int c = it.c0; c < it.c1; c++) havg[0] += f[(long)c * d.nens] * r_nx_ny;
   }
+  seg_combine<1>(havg, sm);
   const double ztop = zint[(long)d.nz * d.nens + e];
   const double rel_dist = (ztop - zmid[(long)k * d.nens + e]) / (ztop - zmid[(long)(d.nz - 1 - (num_layers - 1)) * d.nens + e]);
   const double space_factor = (cos(M_PI * rel_dist) + 1) / 2;
   const double factor = space_factor * time_factor;
-  for (int c = 0; c < nh; c++) {
+  if (!it.active) return;
+  for (int c = it.c0; c < it.c1; c++) {
     const double x = f[(long)c * d.nens];
-    f[(long)c * d.nens] = x + (havg - x) * factor;
+    f[(long)c * d.nens] = x + (havg[0] - x) * factor;
   }
 }
 
@@ -71,42 +111,43 @@ __global__ void __launch_bounds__(128) k_sponge(const Dims d, double *const *fie
 // modules::compute_gcm_forcing_tendencies (gcm_forcing.h:18-205). One thread = (level, member): the ten column
 // means (:103-131) and the fourteen tendencies (:171-203).
 // ---------------------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(128) k_gcm_forcing_compute(const Dims d, const pamm_crm_fields c, const pamm_gcm_columns g,
-                                                             const pamm_forcing_tend t, double r_dt_gcm) {
-  const int e = blockIdx.x * blockDim.x + threadIdx.x;
-  const int k = blockIdx.y;
-  if (e >= d.nens) return;
+__global__ void __launch_bounds__(32 * SEG_MAX) k_gcm_forcing_compute(const Dims d, const pamm_crm_fields c, const pamm_gcm_columns g,
+                                                                      const pamm_forcing_tend t, double r_dt_gcm) {
+  __shared__ double sm[10 * SEG_MAX * 32];
+  const SegItem it = seg_item(d);
+  const int e = it.e, k = blockIdx.y;
   const long base = (long)k * d.ny * d.nx * d.nens + e;
-  const int nh = d.ny * d.nx;
   const double r_nx_ny = 1.0 / (d.nx * d.ny);
-  double a_rd = 0, a_u = 0, a_v = 0, a_t = 0, a_qv = 0, a_ql = 0, a_qi = 0, a_nc = 0, a_ni = 0, a_nr = 0;
-  for (int cc = 0; cc < nh; cc++) {
+  double a[10] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0};      // rd, u, v, t, qv, ql, qi, nc, ni, nr
+  for (int cc = it.c0; cc < it.c1; cc++) {
     const long i = base + (long)cc * d.nens;
     const double rd = c.density_dry[i], rv = c.water_vapor[i];
-    a_rd += rd * r_nx_ny;
-    a_u += c.uvel[i] * r_nx_ny;
-    a_v += c.vvel[i] * r_nx_ny;
-    a_t += c.temp[i] * r_nx_ny;
-    a_qv += (rv / (rd + rv)) * r_nx_ny;
-    a_ql += (c.cloud_water[i] / (rd + rv)) * r_nx_ny;
-    a_qi += (c.ice[i] / (rd + rv)) * r_nx_ny;
-    a_nc += c.cloud_water_num[i] * r_nx_ny;
-    a_ni += c.ice_num[i] * r_nx_ny;
-    a_nr += c.rain_num[i] * r_nx_ny;
+    a[0] += rd * r_nx_ny;
+    a[1] += c.uvel[i] * r_nx_ny;
+    a[2] += c.vvel[i] * r_nx_ny;
+    a[3] += c.temp[i] * r_nx_ny;
+    a[4] += (rv / (rd + rv)) * r_nx_ny;
+    a[5] += (c.cloud_water[i] / (rd + rv)) * r_nx_ny;
+    a[6] += (c.ice[i] / (rd + rv)) * r_nx_ny;
+    a[7] += c.cloud_water_num[i] * r_nx_ny;
+    a[8] += c.ice_num[i] * r_nx_ny;
+    a[9] += c.rain_num[i] * r_nx_ny;
   }
+  seg_combine<10>(a, sm);
+  if (!it.active || threadIdx.y != 0) return;
   const long ke = (long)k * d.nens + e;
   const double grd = g.gcm_density_dry[ke], grv = g.gcm_water_vapor[ke];
-  t.rho_d[ke] = (grd - a_rd) * r_dt_gcm;
-  t.uvel[ke] = (g.gcm_uvel[ke] - a_u) * r_dt_gcm;
-  t.vvel[ke] = (g.gcm_vvel[ke] - a_v) * r_dt_gcm;
-  t.temp[ke] = (g.gcm_temp[ke] - a_t) * r_dt_gcm;
-  const double fqv = (grv / (grd + grv) - a_qv) * r_dt_gcm;
-  const double fql = (g.gcm_cloud_water[ke] / (grd + grv) - a_ql) * r_dt_gcm;
-  const double fqi = (g.gcm_cloud_ice[ke] / (grd + grv) - a_qi) * r_dt_gcm;
+  t.rho_d[ke] = (grd - a[0]) * r_dt_gcm;
+  t.uvel[ke] = (g.gcm_uvel[ke] - a[1]) * r_dt_gcm;
+  t.vvel[ke] = (g.gcm_vvel[ke] - a[2]) * r_dt_gcm;
+  t.temp[ke] = (g.gcm_temp[ke] - a[3]) * r_dt_gcm;
+  const double fqv = (grv / (grd + grv) - a[4]) * r_dt_gcm;
+  const double fql = (g.gcm_cloud_water[ke] / (grd + grv) - a[5]) * r_dt_gcm;
+  const double fqi = (g.gcm_cloud_ice[ke] / (grd + grv) - a[6]) * r_dt_gcm;
   t.qv[ke] = fqv; t.ql[ke] = fql; t.qi[ke] = fqi;
-  t.nc[ke] = (g.gcm_num_liq[ke] - a_nc) * r_dt_gcm;
-  t.ni[ke] = (g.gcm_num_ice[ke] - a_ni) * r_dt_gcm;
-  t.nr[ke] = (g.gcm_num_rain[ke] - a_nr) * r_dt_gcm;
+  t.nc[ke] = (g.gcm_num_liq[ke] - a[7]) * r_dt_gcm;
+  t.ni[ke] = (g.gcm_num_ice[ke] - a[8]) * r_dt_gcm;
+  t.nr[ke] = (g.gcm_num_rain[ke] - a[9]) * r_dt_gcm;
   t.qtot[ke] = fqv + fql + fqi;
 }
 
@@ -120,45 +161,23 @@ __global__ void __launch_bounds__(128) k_gcm_forcing_compute(const Dims d, const
 // the fill is the identity (x - 0*factor/dz), so deciding per thread gives the same result without a host sync.
 // neg/pos are kept for the whole-CRM stage below.
 // ---------------------------------------------------------------------------------------------------------------
-__device__ __forceinline__ void level_fill(double *x, long base, int nh, int nens, double dzk, double neg, double &pos_out) {
-  double pos = 0.0;
-  for (int cc = 0; cc < nh; cc++) {
-    const double v = x[base + (long)cc * nens];
-    if (v > 0) pos += v * dzk;
-  }
-  pos_out = pos;
-  if (pos > 0) {
-    for (int cc = 0; cc < nh; cc++) {
-      const long i = base + (long)cc * nens;
-      const double v = x[i];
-      const double factor = v * dzk / pos;
-      x[i] = fmax(0.0, v - (neg * factor) / dzk);
-    }
-  }
-}
-
-__global__ void __launch_bounds__(128) k_gcm_forcing_apply(const Dims d, const pamm_crm_fields c, const pamm_gcm_columns g,
-                                                           const pamm_forcing_tend t, const double *dz, double dt, double r_dt_gcm,
-                                                           double *scratch) {
-  const int e = blockIdx.x * blockDim.x + threadIdx.x;
-  const int k = blockIdx.y;
-  if (e >= d.nens) return;
+__global__ void __launch_bounds__(32 * SEG_MAX) k_gcm_forcing_apply(const Dims d, const pamm_crm_fields c, const pamm_gcm_columns g,
+                                                                    const pamm_forcing_tend t, const double *dz, double dt, double r_dt_gcm,
+                                                                    double *scratch) {
+  __shared__ double sm[6 * SEG_MAX * 32];
+  const SegItem it = seg_item(d);
+  const int e = it.e, k = blockIdx.y;
   const long base = (long)k * d.ny * d.nx * d.nens + e;
   const long ke = (long)k * d.nens + e;
-  const int nh = d.ny * d.nx;
   const double r_nx_ny = 1.0 / (d.nx * d.ny);
   const double f_rd = t.rho_d[ke], f_u = t.uvel[ke], f_v = t.vvel[ke], f_t = t.temp[ke];
   const double f_qv = t.qv[ke], f_ql = t.ql[ke], f_qi = t.qi[ke], f_nc = t.nc[ke], f_ni = t.ni[ke], f_nr = t.nr[ke];
   const double dzk = dz[ke];
-  double avg_v = 0, avg_l = 0, avg_i = 0, neg_v = 0, neg_l = 0, neg_i = 0;
-  for (int cc = 0; cc < nh; cc++) {
+  double a[6] = {0, 0, 0, 0, 0, 0};       // avg_v, avg_l, avg_i, neg_v, neg_l, neg_i
+  for (int cc = it.c0; cc < it.c1; cc++) {
     const long i = base + (long)cc * d.nens;
     const double rho_d_old = c.density_dry[i];
     const double rd = rho_d_old + f_rd * dt;
-    c.density_dry[i] = rd;
-    c.uvel[i] += f_u * dt;
-    c.vvel[i] += f_v * dt;
-    c.temp[i] += f_t * dt;
     double rv = c.water_vapor[i], rl = c.cloud_water[i], ri = c.ice[i];
     const double qv_new = rv / (rho_d_old + rv) + f_qv * dt;
     const double ql_new = rl / (rho_d_old + rv) + f_ql * dt;
@@ -170,24 +189,61 @@ __global__ void __launch_bounds__(128) k_gcm_forcing_apply(const Dims d, const p
     if (xc < 0) xc = 0;
     if (xi < 0) xi = 0;
     if (xr < 0) xr = 0;
-    c.cloud_water_num[i] = xc; c.ice_num[i] = xi; c.rain_num[i] = xr;
-    avg_v += rv * r_nx_ny; avg_l += rl * r_nx_ny; avg_i += ri * r_nx_ny;
-    if (rv < 0) { neg_v += -rv * dzk; rv = 0; }
-    if (rl < 0) { neg_l += -rl * dzk; rl = 0; }
-    if (ri < 0) { neg_i += -ri * dzk; ri = 0; }
-    c.water_vapor[i] = rv; c.cloud_water[i] = rl; c.ice[i] = ri;
+    a[0] += rv * r_nx_ny; a[1] += rl * r_nx_ny; a[2] += ri * r_nx_ny;
+    if (rv < 0) { a[3] += -rv * dzk; rv = 0; }
+    if (rl < 0) { a[4] += -rl * dzk; rl = 0; }
+    if (ri < 0) { a[5] += -ri * dzk; ri = 0; }
+    if (it.active) {
+      c.density_dry[i] = rd;
+      c.uvel[i] += f_u * dt;
+      c.vvel[i] += f_v * dt;
+      c.temp[i] += f_t * dt;
+      c.cloud_water_num[i] = xc; c.ice_num[i] = xi; c.rain_num[i] = xr;
+      c.water_vapor[i] = rv; c.cloud_water[i] = rl; c.ice[i] = ri;
+    }
   }
-  t.rho_v[ke] = (g.gcm_water_vapor[ke] - avg_v) * r_dt_gcm;
-  t.rho_l[ke] = (g.gcm_cloud_water[ke] - avg_l) * r_dt_gcm;
-  t.rho_i[ke] = (g.gcm_cloud_ice[ke] - avg_i) * r_dt_gcm;
-  const long nke = (long)d.nz * d.nens;
-  double pos_v = 0, pos_l = 0, pos_i = 0;
-  if (neg_v > 0) level_fill(c.water_vapor, base, nh, d.nens, dzk, neg_v, pos_v);
-  if (neg_l > 0) level_fill(c.cloud_water, base, nh, d.nens, dzk, neg_l, pos_l);
-  if (neg_i > 0) level_fill(c.ice, base, nh, d.nens, dzk, neg_i, pos_i);
-  scratch[0 * nke + ke] = neg_v; scratch[1 * nke + ke] = pos_v;
-  scratch[2 * nke + ke] = neg_l; scratch[3 * nke + ke] = pos_l;
-  scratch[4 * nke + ke] = neg_i; scratch[5 * nke + ke] = pos_i;
+  seg_combine<6>(a, sm);
+  const bool lead = it.active && threadIdx.y == 0;
+  if (lead) {
+    t.rho_v[ke] = (g.gcm_water_vapor[ke] - a[0]) * r_dt_gcm;
+    t.rho_l[ke] = (g.gcm_cloud_water[ke] - a[1]) * r_dt_gcm;
+    t.rho_i[ke] = (g.gcm_cloud_ice[ke] - a[2]) * r_dt_gcm;
+  }
+  // level stage of fill_holes (gcm_forcing.h:208-255) for the species that went negative somewhere on this (level, member):
+  // the positive mass available on the level, then every cell gives up its share. Whether ANY column of the block needs it
+  // is a block-wide decision (the barriers inside seg_combine); a column that does not need it only lends its threads.
+  double *const xs[3] = {c.water_vapor, c.cloud_water, c.ice};
+  double pos[3] = {0, 0, 0};
+  const bool need_any = a[3] > 0 || a[4] > 0 || a[5] > 0;
+  if (__syncthreads_or(need_any ? 1 : 0)) {
+#pragma unroll
+    for (int sp = 0; sp < 3; sp++) {
+      if (!(a[3 + sp] > 0)) continue;
+      for (int cc = it.c0; cc < it.c1; cc++) {
+        const double v = xs[sp][base + (long)cc * d.nens];
+        if (v > 0) pos[sp] += v * dzk;
+      }
+    }
+    seg_combine<3>(pos, sm);
+    if (it.active) {
+#pragma unroll
+      for (int sp = 0; sp < 3; sp++) {
+        if (!(a[3 + sp] > 0) || !(pos[sp] > 0)) continue;
+        for (int cc = it.c0; cc < it.c1; cc++) {
+          const long i = base + (long)cc * d.nens;
+          const double v = xs[sp][i];
+          const double factor = v * dzk / pos[sp];
+          xs[sp][i] = fmax(0.0, v - (a[3 + sp] * factor) / dzk);
+        }
+      }
+    }
+  }
+  if (lead) {
+    const long nke = (long)d.nz * d.nens;
+    scratch[0 * nke + ke] = a[3]; scratch[1 * nke + ke] = pos[0];
+    scratch[2 * nke + ke] = a[4]; scratch[3 * nke + ke] = pos[1];
+    scratch[4 * nke + ke] = a[5]; scratch[5 * nke + ke] = pos[2];
+  }
 }
 
 // Whole-CRM stage of fill_holes (gcm_forcing.h:257-289): one thread = (member, species). The mass a level could not pay
@@ -325,8 +381,8 @@ int pamm_sponge_layer(pamm_workspace *w, double *const *fields, int num_fields, 
   }
   PCK(cudaMemcpyAsync(w->fptr_d, fields, sizeof(double *) * num_fields, cudaMemcpyHostToDevice, w->stream));
   const Dims d{w->nz, w->ny, w->nx, w->nens};
-  const dim3 grid((unsigned)(w->nens + 127) / 128, (unsigned)num_layers, (unsigned)num_fields);
-  k_sponge<<<grid, 128, 0, w->stream>>>(d, w->fptr_d, num_fields, num_layers, zint, zmid, crm_dt / time_scale);
+  const dim3 grid((unsigned)(w->nens + 31) / 32, (unsigned)num_layers, (unsigned)num_fields);
+  k_sponge<<<grid, dim3(32, seg_count(w->ny * w->nx)), 0, w->stream>>>(d, w->fptr_d, num_fields, num_layers, zint, zmid, crm_dt / time_scale);
   w->launches++;
   PCK(cudaGetLastError());
   return 0;
@@ -336,8 +392,8 @@ int pamm_compute_gcm_forcing_tendencies(pamm_workspace *w, const pamm_crm_fields
                                         const pamm_forcing_tend *tend, double gcm_physics_dt) {
   if (!(gcm_physics_dt > 0.0)) { w->err = "pamm_compute_gcm_forcing_tendencies: gcm_physics_dt must be positive"; return 1; }
   const Dims d{w->nz, w->ny, w->nx, w->nens};
-  const dim3 grid((unsigned)(w->nens + 127) / 128, (unsigned)w->nz);
-  k_gcm_forcing_compute<<<grid, 128, 0, w->stream>>>(d, *crm, *gcm, *tend, 1.0 / gcm_physics_dt);
+  const dim3 grid((unsigned)(w->nens + 31) / 32, (unsigned)w->nz);
+  k_gcm_forcing_compute<<<grid, dim3(32, seg_count(w->ny * w->nx)), 0, w->stream>>>(d, *crm, *gcm, *tend, 1.0 / gcm_physics_dt);
   w->launches++;
   PCK(cudaGetLastError());
   return 0;
@@ -347,8 +403,8 @@ int pamm_apply_gcm_forcing_tendencies(pamm_workspace *w, const pamm_crm_fields *
                                       const pamm_forcing_tend *tend, const double *dz, double crm_dt, double gcm_physics_dt) {
   if (!(gcm_physics_dt > 0.0)) { w->err = "pamm_apply_gcm_forcing_tendencies: gcm_physics_dt must be positive"; return 1; }
   const Dims d{w->nz, w->ny, w->nx, w->nens};
-  const dim3 grid((unsigned)(w->nens + 127) / 128, (unsigned)w->nz);
-  k_gcm_forcing_apply<<<grid, 128, 0, w->stream>>>(d, *crm, *gcm, *tend, dz, crm_dt, 1.0 / gcm_physics_dt, w->scratch);
+  const dim3 grid((unsigned)(w->nens + 31) / 32, (unsigned)w->nz);
+  k_gcm_forcing_apply<<<grid, dim3(32, seg_count(w->ny * w->nx)), 0, w->stream>>>(d, *crm, *gcm, *tend, dz, crm_dt, 1.0 / gcm_physics_dt, w->scratch);
   k_fill_holes_global<<<dim3((unsigned)(w->nens + 127) / 128, 3), 128, 0, w->stream>>>(d, crm->water_vapor, crm->cloud_water, crm->ice, dz,
                                                                                        w->scratch);
   w->launches += 2;

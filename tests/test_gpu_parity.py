@@ -481,3 +481,32 @@ def test_scratch_memory_is_never_read_before_it_is_written_and_steps_repeat_bit_
             assert np.array_equal(a, b)
     for k, a in zip(list(H.STATE_FIELDS) + [t[0] for t in case["tracers"]], runs[0][3]):
         assert np.array_equal(a, runs[0][2][k]), k       # host path == resident path
+
+
+@pytest.mark.parametrize("nt", [1, 10])
+def test_paged_vertical_table_gives_the_bits_of_the_global_table(nt, monkeypatch):
+    """ord 9 at 40 levels: the per-level table (42 x 206 doubles) does not fit the constant bank as a whole, so the z marches
+    run segment by segment behind the upload of the levels each segment reads (table home 4). Same numbers, same
+    arithmetic as the global-memory table (home 3): identical bits, through the resident step, the tendency entry point
+    and the host-buffer entry point (whose slabs, on several streams, read the global copy)."""
+    import torch
+    case = _case(nz=40, nx=10, nens=40, nt=nt)
+    out = {}
+    for no_page in ("0", "1"):
+        if no_page == "1":
+            monkeypatch.setenv("AWFL_NO_CVPAGE", "1")
+        c, d = H.make_gpu(case, 9, crm_dt=2.0)
+        assert d.table_home() == (3 if no_page == "1" else 4)
+        d.declare_current_profile_as_hydrostatic(c)
+        names = list(H.STATE_FIELDS) + c.get_tracer_names()
+        host = [np.ascontiguousarray(case["fields"][n]).copy() for n in names]
+        d.timeStep(c); d.timeStep(c)
+        d.set_host_slabs(2)
+        d.time_step_host(host, 2.0); d.time_step_host(host, 2.0)
+        got = H.gpu_fields(c)
+        for n, a in zip(names, host):
+            assert np.array_equal(a, got[n]), n
+        out[no_page] = got
+        d.finalize()
+    for k in out["0"]:
+        assert np.array_equal(out["0"][k], out["1"][k]), k

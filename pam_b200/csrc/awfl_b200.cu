@@ -940,7 +940,8 @@ static void launch_tracer_sweep(awfl_handle *h, const Geom &g, int dir, TracerSw
   if (g.nt == 0) return;
   // the grid carries (tracer, line index, segment) in blockIdx.z, which CUDA limits to 65535: tall grids with many tracers
   // (nz = 128, nx >= 768: 2048 work items per tracer) go in chunks of tracers
-  int per_launch = 65535 >> (a.labits + a.sbits);
+  static const int zmax = getenv("AWFL_GRID_Z_MAX") && atoi(getenv("AWFL_GRID_Z_MAX")) > 0 ? atoi(getenv("AWFL_GRID_Z_MAX")) : 65535;   // tests
+  int per_launch = zmax >> (a.labits + a.sbits);
   if (per_launch < 1) per_launch = 1;
   for (int t0 = 0; t0 < g.nt; t0 += per_launch) {
     a.tr0 = t0; a.ntr = g.nt - t0 < per_launch ? g.nt - t0 : per_launch;

@@ -510,3 +510,36 @@ def test_paged_vertical_table_gives_the_bits_of_the_global_table(nt, monkeypatch
         d.finalize()
     for k in out["0"]:
         assert np.array_equal(out["0"][k], out["1"][k]), k
+
+
+def test_tracer_marches_in_chunks_give_the_same_bits():
+    """blockIdx.z of a tracer march carries (tracer, line index, segment) and is limited to 65535: tall grids with many
+    tracers are launched in chunks of tracers. Forced here on a small case (AWFL_GRID_Z_MAX, read once per process: run in
+    a process of its own): 10 tracers in chunks of 4, 4, 2 against one launch."""
+    import subprocess, sys, os
+    code = r'''
+import sys, numpy as np
+sys.path.insert(0, "tests")
+import helpers as H
+from pam_b200 import synthetic as syn
+case = syn.make_case(12, 4, 10, 33, tracers=syn.TRACERS_P3_SHOC, grid="tanh")
+c, d = H.make_gpu(case, 5, crm_dt=2.0)
+d.declare_current_profile_as_hydrostatic(c)
+n0 = d.launch_count(); d.timeStep(c); d.timeStep(c)
+f = H.gpu_fields(c)
+np.savez(sys.argv[1], launches=d.launch_count() - n0, **f)
+'''
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    outs = []
+    for zmax in ("", "64"):
+        path = os.path.join("/tmp", "awfl_chunk_%s.npz" % (zmax or "all"))
+        env = dict(os.environ)
+        if zmax:
+            env["AWFL_GRID_Z_MAX"] = zmax
+        r = subprocess.run([sys.executable, "-c", code, path], cwd=root, env=env, capture_output=True, text=True)
+        assert r.returncode == 0, r.stderr[-2000:]
+        outs.append(np.load(path))
+    assert int(outs[1]["launches"]) > int(outs[0]["launches"])
+    for k in outs[0].files:
+        if k != "launches":
+            assert np.array_equal(outs[0][k], outs[1][k]), k

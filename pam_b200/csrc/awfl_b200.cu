@@ -77,6 +77,20 @@ __device__ __forceinline__ double rcp_pos_b(double x) {   // same as awfl_weno.c
   return fma(r, fma(e, e, e), r);
 }
 
+// max(x, 0) and min(x, 0) of the FCT mass budget as arithmetic: x + |x| = 2 max(x, 0) and x - |x| = 2 min(x, 0) EXACTLY,
+// and the factor 2 is folded into the constant that multiplies the difference anyway (a power of two: the same bits as
+// (max - min) * c). fmax / fmin of doubles compile to 7-instruction compare / select / move sequences (their NaN rule);
+// in the fused FCT kernel they were 42 % of all non-FP64 instructions (profiles/r02s_fct_line_mix.txt), and that kernel
+// is issue-bound (68 % issue-active at 51 % of the HBM rate).
+__device__ __forceinline__ double pos2(double x) { return x + fabs(x); }
+__device__ __forceinline__ double neg2(double x) { return x - fabs(x); }
+// avail / out for out > avail >= 0 (else 1): reciprocal-multiply (MUFU seed + one cubic step, <= 1 ulp, no divergent slow
+// path); + 1e-290 keeps the seed in the normal range (a no-op for out > 1e-274; below it avail < out and the product < 1)
+__device__ __forceinline__ double fct_multiplier(double avail, double out) {
+  const double m = avail * rcp_pos_b(out + 1.0e-290);
+  return out > avail ? m : 1.0;
+}
+
 __global__ void __launch_bounds__(256) k_fct_mult(const Geom g, const FctArgs a, const RowMap rm) {
   long cell; int k, j, i, e;
   if (!row_coords(g, rm, cell, k, j, i, e)) return;
@@ -93,21 +107,20 @@ __global__ void __launch_bounds__(256) k_fct_mult(const Geom g, const FctArgs a,
       if (a.sb != 0.0) start = a.sa * start + a.sb * __ldg(a.qs + (NS + tr) * nc + cell);
     }
     const double vol = g.dx * g.dy * dzk;
-    const double avail = fmax(start, 0.0) * vol;
+    const double avail = pos2(start) * (0.5 * vol);
     const double *fx = a.tfx + tr * nc, *fz = a.tfz + tr * (nc + sz);
     const double fx0 = __ldg(fx + cell), fx1 = __ldg(fx + (i == g.nx - 1 ? cell - (long)(g.nx - 1) * sx : cell + sx));
-    const double ox = (fmax(fx1, 0.0) - fmin(fx0, 0.0)) * a.rdx;
+    const double ox = (pos2(fx1) - neg2(fx0)) * (0.5 * a.rdx);
     double oy = 0.0;
     if (!g.sim2d) {
       const double *fy = a.tfy + tr * nc;
       const double fy0 = __ldg(fy + cell), fy1 = __ldg(fy + (j == g.ny - 1 ? cell - (long)(g.ny - 1) * sy : cell + sy));
-      oy = (fmax(fy1, 0.0) - fmin(fy0, 0.0)) * a.rdy;
+      oy = (pos2(fy1) - neg2(fy0)) * (0.5 * a.rdy);
     }
     const double fz0 = __ldg(fz + cell), fz1 = __ldg(fz + cell + sz);
-    const double oz = (fmax(fz1, 0.0) - fmin(fz0, 0.0)) * rdzk;
+    const double oz = (pos2(fz1) - neg2(fz0)) * (0.5 * rdzk);
     const double out = (ox + oy + oz) * a.dt * vol;
-    // reciprocal-multiply (<= 1 ulp, no divergent slow path); the clamp keeps the seed in the normal range
-    if (out > avail) mult = avail * rcp_pos_b(fmax(out, 1.0e-290));
+    mult = fct_multiplier(avail, out);
   }
   a.mult[tr * nc + cell] = mult;
 }
@@ -126,9 +139,10 @@ struct TracerUpdArgs {
 
 // scaled flux through an interface: F>0 leaves the low-side cell, F<0 leaves the high-side cell
 __device__ __forceinline__ double fct_scaled(double F, double mult_lo, double mult_hi, bool seam) {
-  if (F > 0.0) return F * mult_lo;
-  if (F < 0.0 && !seam) return F * mult_hi;
-  return F;   // periodic seam with F<0: min() of the two edge copies selects the unscaled one (Dycore.h:574-579)
+  // F == 0 takes either factor (0 * m = 0); periodic seam with F < 0: min() of the two edge copies selects the unscaled one
+  // (Dycore.h:574-579). A select and a product, no branch.
+  const double m = F > 0.0 ? mult_lo : (seam ? 1.0 : mult_hi);
+  return F * m;
 }
 
 __global__ void __launch_bounds__(256) k_tracer_update(const Geom g, const TracerUpdArgs a, const RowMap rm) {
@@ -164,7 +178,7 @@ __global__ void __launch_bounds__(256) k_tracer_update(const Geom g, const Trace
   double v = a.b * ts;
   if (a.a != 0.0) v = fma(a.a, a.q0[(NS + tr) * nc + cell], v);   // plain load: qout may alias q0
   v += a.c * tend;
-  if (a.positive[tr]) v = fmax(0.0, v);
+  if (a.positive[tr]) v = 0.5 * pos2(v);
   a.qout[(NS + tr) * nc + cell] = v;
 }
 
@@ -237,18 +251,16 @@ __global__ void __launch_bounds__(32, W <= 4 ? 16 : 10) k_fct_update_2d(const Ge
 #pragma unroll
         for (int c = 0; c < W + 2; c++) V[c] = fma(a.a, q0k[off[c]], V[c]);   // plain load: qout may alias q0
       }
-      const double vol = g.dx * g.dy * dzk;
+      const double vol = g.dx * g.dy * dzk, hrdx = 0.5 * a.rdx;
 #pragma unroll
       for (int c = 0; c < W + 2; c++) {
         double m = 1.0;
         if (positive) {
-          const double avail = fmax(V[c], 0.0) * vol;
-          const double ox = (fmax(X[c + 1], 0.0) - fmin(X[c], 0.0)) * a.rdx;
-          const double oz = (fmax(B[c], 0.0) - fmin(A[c], 0.0)) * rdzk;
+          const double avail = pos2(V[c]) * (0.5 * vol);
+          const double ox = (pos2(X[c + 1]) - neg2(X[c])) * hrdx;
+          const double oz = (pos2(B[c]) - neg2(A[c])) * (0.5 * rdzk);
           const double out = (ox + oz) * a.dt * vol;
-          // avail/out as a reciprocal-multiply (MUFU seed + one cubic step, <= 1 ulp; no divergent slow path). The clamp
-          // keeps the seed in the normal range; below it avail < out < 1e-290 and the product is still < 1.
-          if (out > avail) m = avail * rcp_pos_b(fmax(out, 1.0e-290));
+          m = fct_multiplier(avail, out);
         }
         M[c] = m;
       }
@@ -268,7 +280,7 @@ __global__ void __launch_bounds__(32, W <= 4 ? 16 : 10) k_fct_update_2d(const Ge
       const double hA = fct_scaled(A[c + 1], kk > 0 ? Mp[c] : 1.0, M[c + 1], false);
       if (finish) {
         double v = fma(-crdz_prev, hA, P[c]);
-        if (positive) v = fmax(0.0, v);
+        if (positive) v = 0.5 * pos2(v);
         qok[off[c + 1]] = v;
       }
       if (start) {

@@ -1016,7 +1016,9 @@ static void run_stage(awfl_handle *h, const Geom &g, const double *qin, const do
   }
   if (g.nt > 0 && g.sim2d && mode == 1 && !fct_start && h->fused_fct) {
     // fused FCT + update (2-D): strips of W columns, enough level segments for a few waves of one-warp blocks
-    constexpr int W = AWFL_FCT_STRIP;
+    // W = 4, or 8 where the strips divide the line (6 halo-inclusive multipliers per 4 results against 10 per 8: 7.21 -> 7.01 ms
+    // at C5; ragged strips lose it again, profiles/r02u_fct_variants.txt)
+    const int W = (g.nx % 8 == 0 && g.nx >= 16) ? 8 : AWFL_FCT_STRIP;
     FctUpdArgs u;
     u.q0 = q0; u.qs = qin; u.qout = qout; u.tfx = h->tflux[0]; u.tfz = h->tflux[2]; u.dz = h->dz; u.rdz = h->rdz;
     u.positive = h->positive_d; u.a = a; u.b = b; u.c = b * dt_full; u.dt = dt_stage; u.rdx = 1.0 / g.dx;
@@ -1028,7 +1030,8 @@ static void run_stage(awfl_handle *h, const Geom &g, const double *qin, const do
     if (const char *ev = getenv("AWFL_FCT_KSEGS")) { const int v = atoi(ev); if (v >= 1 && v <= g.nz) ks = v; }   // experiments
     u.ksegs = (int)ks;
     ProfScope ps(h, KC_TRACER_UPD);
-    k_fct_update_2d<W><<<dim3(tiles, strips, (unsigned)(g.nt * ks)), 32, 0, h->stream>>>(g, u);
+    if (W == 8) k_fct_update_2d<8><<<dim3(tiles, strips, (unsigned)(g.nt * ks)), 32, 0, h->stream>>>(g, u);
+    else k_fct_update_2d<AWFL_FCT_STRIP><<<dim3(tiles, strips, (unsigned)(g.nt * ks)), 32, 0, h->stream>>>(g, u);
   } else if (g.nt > 0) {
     const RowMap rm = row_map(g, 256);
     const unsigned blocks = row_blocks(g, rm);

@@ -4,6 +4,8 @@ into hand-written sm_100a kernels. No torch ops, no numpy and no oracle on this 
 the import of this module's compute entry points raises (no CPU fallback).
 """
 import ctypes as C
+import os
+
 import numpy as np
 import torch
 
@@ -169,8 +171,17 @@ class Dycore:
         """Dycore::timeStep (Dycore.h:107-255). ncycles>0 fixes the sub-cycle count (no host sync). Returns ncycles."""
         f, keep = self._fields(coupler)
         n = C.c_int(0)
+        debug = bool(os.environ.get("PAM_DEBUG"))          # the reference's compile-time PAM_DEBUG (Dycore.h:136-138,224-251)
+        mass_init = self.compute_mass(coupler) if debug else None
         self._rc(self.lib.awfl_time_step(self.h, C.byref(f), float(coupler.get_option("crm_dt")), int(ncycles), C.byref(n)),
                  "awfl_time_step")
+        if debug:
+            mass_final = self.compute_mass(coupler)
+            diff = mass_final - mass_init
+            rel = np.abs(diff) / (np.abs(mass_init) + 1.e-20)
+            for ivar, iens in zip(*np.nonzero((rel > 1.e-10) & (np.abs(diff) > 1.e-10))):
+                print("WARNING: conservation violated variable,ensemble,rel_diff,mass_diff,init,final: %d , %d , %10.6e , %10.6e , %10.6e , %10.6e"
+                      % (ivar, iens, rel[ivar, iens], diff[ivar, iens], mass_init[ivar, iens], mass_final[ivar, iens]))
         return n.value
 
     def compute_time_step(self, coupler, cfl=0.8):

@@ -253,12 +253,13 @@ def test_host_buffer_member_slabs_are_bit_identical(nens, slabs, ny):
         assert np.array_equal(a, got[n]), n
 
 
-@pytest.mark.parametrize("nx,nz,nens", [(10, 12, 40), (5, 9, 33), (24, 20, 64)])
+@pytest.mark.parametrize("nx,nz,nens", [(10, 12, 40), (5, 9, 33), (24, 20, 64), (16, 12, 40)])
 def test_fused_fct_update_matches_two_kernel_path(nx, nz, nens, monkeypatch):
     """2-D: the fused FCT + tracer update strip march (k_fct_update_2d) against the two cell-local kernels it replaces
     (k_fct_mult + k_tracer_update, still the 3-D path): same formulas, different summation order -> equal to round-off.
     P3+SHOC tracer set with exact zeros over a third of the cells so that the limiter actually scales fluxes; strips that
-    are ragged (nx not a multiple of 8) or wider than the domain (nx < 8) and level segments are exercised."""
+    are ragged (nx not a multiple of 4) or wider than the domain (nx < 4), the 8-column strips of lines they divide (nx = 16,
+    24) and level segments are exercised."""
     case = syn.make_case(nz, 1, nx, nens, tracers=syn.TRACERS_P3_SHOC, grid="tanh")
     out = {}
     for fused in ("1", "0"):

@@ -1018,7 +1018,8 @@ static void run_stage(awfl_handle *h, const Geom &g, const double *qin, const do
     // fused FCT + update (2-D): strips of W columns, enough level segments for a few waves of one-warp blocks
     // W = 4, or 8 where the strips divide the line (6 halo-inclusive multipliers per 4 results against 10 per 8: 7.21 -> 7.01 ms
     // at C5; ragged strips lose it again, profiles/r02u_fct_variants.txt)
-    const int W = (g.nx % 8 == 0 && g.nx >= 16) ? 8 : AWFL_FCT_STRIP;
+    // (with few tracers the narrower strips' larger grid wins: C2, one tracer, 0.90 against 0.93 ms)
+    const int W = (g.nx % 8 == 0 && g.nx >= 16 && g.nt >= 4) ? 8 : AWFL_FCT_STRIP;
     FctUpdArgs u;
     u.q0 = q0; u.qs = qin; u.qout = qout; u.tfx = h->tflux[0]; u.tfz = h->tflux[2]; u.dz = h->dz; u.rdz = h->rdz;
     u.positive = h->positive_d; u.a = a; u.b = b; u.c = b * dt_full; u.dt = dt_stage; u.rdx = 1.0 / g.dx;

@@ -253,7 +253,7 @@ def test_host_buffer_member_slabs_are_bit_identical(nens, slabs, ny):
         assert np.array_equal(a, got[n]), n
 
 
-@pytest.mark.parametrize("nx,nz,nens", [(10, 12, 40), (5, 9, 33), (24, 20, 64), (16, 12, 40)])
+@pytest.mark.parametrize("nx,nz,nens", [(10, 12, 40), (5, 9, 33), (24, 20, 64), (16, 12, 40)])   # P3+SHOC set: 10 tracers -> 8-column strips at nx = 16, 24
 def test_fused_fct_update_matches_two_kernel_path(nx, nz, nens, monkeypatch):
     """2-D: the fused FCT + tracer update strip march (k_fct_update_2d) against the two cell-local kernels it replaces
     (k_fct_mult + k_tracer_update, still the 3-D path): same formulas, different summation order -> equal to round-off.

@@ -3,12 +3,14 @@
 //
 // Design: the reference materialises two haloed state copies, a pressure array and six flux arrays
 // per Runge-Kutta stage and launches ~10 generic one-thread-per-index kernels. Here the dycore state lives UN-haloed
-// in three persistent buffers; per stage and per direction ONE "sweep" kernel marches each warp along a line segment
-// with the stencil window held in registers (32 lanes = 32 consecutive ensemble members, so every global access is a
-// coalesced 256-byte line), fusing primitive recovery, pressure, periodic wrap / wall boundary conditions, WENO
+// in three persistent buffers; per stage and per direction ONE marching kernel (awfl_march.cuh) walks each warp along a
+// line with the stencil window in a shared-memory ring (32 lanes = 32 consecutive ensemble members, so every global access
+// is a coalesced 256-byte line), fusing primitive recovery, pressure, periodic wrap / wall boundary conditions, WENO
 // reconstruction, the characteristic Riemann solve, the upwind advective fluxes and the flux divergence; the last
-// sweep of a stage also applies gravity and the SSPRK3 stage combination. Tracers ride on the stored interface
-// mass flux in a second, lighter sweep; FCT positivity is two cell-local kernels.
+// march of a stage also applies gravity and the SSPRK3 stage combination. Tracers ride on the stored interface
+// mass flux in a second, lighter march; FCT positivity + the tracer update are one strip-marching kernel in 2-D, two
+// cell-local kernels in 3-D. This file holds those tracer kernels, the conversions, the diagnostics, the idealized
+// initial states, the handle and the C ABI; awfl_haloed.cuh the entry points on the reference's haloed arrays.
 //
 // There is NO CPU fallback in this file: every entry point launches kernels or fails.
 #include <cuda_runtime.h>

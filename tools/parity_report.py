@@ -47,7 +47,7 @@ if pamcuda.available("ref", 5):
         d.declare_current_profile_as_hydrostatic(c)
         gv = c.get_data_manager_device_readonly().get("variable_gravity").cpu().numpy()
         res = {}
-        for mode in ("intended", "raw"):
+        for mode in ("raw", "intended"):      # raw FIRST: its haloed arrays then come from pool memory no intended run has pre-filled
             r = pamcuda.PamCudaDycore("ref", case["nz"], case["ny"], case["nx"], case["nens"], case["xlen"], case["ylen"], case["zint"],
                                       tracers=case["tracers"], consts=case["consts"], crm_dt=2.0, ord=ord)
             r.set_fields(case["fields"])

@@ -445,7 +445,7 @@ def main():
     hbm_peak = peaks.get("hbm_gbs", 6650.0)
     hbm_src = "measured (MEASURED_PEAKS.json)" if "hbm_gbs" in peaks else "fallback (B200_PROFILING.md)"
     if dom.startswith("state_"):
-        fl = roofline.state_sweep_flops_per_cell(w["ord"]) * ncell
+        fl = roofline.state_sweep_flops_per_cell(w["ord"], sim2d=w["ny"] == 1) * ncell
         by = roofline.state_sweep_bytes_per_cell(last=dom == "state_z") * ncell
     elif dom.startswith("tracer_") and dom != "tracer_upd":
         fl = (roofline.recon_flops(w["ord"])[0] + 4) * ncell * nt
@@ -479,7 +479,9 @@ def main():
             "note": "the AWFL step is FP64-pipe bound (SURVEY.md 8d: 32-60 flop/B vs a ridge of ~6), so the binding roofline "
                     "is the FP64 one; `achieved` counts the REFERENCE algorithm's flops (pam_b200/roofline.py, frozen from the "
                     "instrumented count of tools/count_flops.py), launch time averaged over all launches of the class in a separate "
-                    "profiling pass; `traffic` and `hbm.bytes_per_launch` describe a stage-2/3 launch of the class"}
+                    "profiling pass; `traffic` and `hbm.bytes_per_launch` describe a stage-2/3 launch of the class. In a 2-D workload the "
+                    "state marches leave out the reconstruction of v, whose flux the reference computes and then discards "
+                    "(Dycore.h:565): those flops are NOT counted in `achieved` (7 reconstructions per cell and direction, not 8)"}
     ms_total = r["ms_per_step"] * args.steps
     step_fl = roofline.flops_per_cell_update(w["ord"], w["nt"], ndir) * float(ncell) * sum(cyc)
     step_by = roofline.bytes_per_cell_update(w["nt"]) * float(ncell) * sum(cyc)

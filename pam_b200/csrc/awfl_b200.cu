@@ -665,6 +665,7 @@ struct awfl_handle {
   double *stage_fields;  // staging buffer for the host-buffer entry point (5+nt fields)
   int host_last_ncycles;      // sub-cycle count derived by the previous awfl_time_step_host (0 = none yet): the prediction
   long host_mispredictions;   // calls whose prediction was wrong and were redone un-overlapped
+  bool general_2d;       // 2-D on the general state marches (AWFL_GENERAL_2D=1; see SweepArgs::general_2d)
   bool fused_fct;        // 2-D: fused FCT + tracer update kernel (AWFL_FUSED_FCT=0 selects the two-kernel path)
   int host_slabs;        // member slabs of the host-buffer entry point (copy/compute overlap); 1 = no pipelining, 0 = auto
   cudaStream_t s_in, s_out;              // copy streams of the host-buffer entry point
@@ -997,7 +998,7 @@ static void run_stage(awfl_handle *h, const Geom &g, const double *qin, const do
     s.qin = qin; s.qbase = q0; s.qout = mode == 2 ? st_out : qout; s.tend = h->tend; s.mflux = h->mflux[dir];
     s.dz = h->dz; s.grav_var = h->grav_var; s.vtab = h->vtab; s.rdz = h->rdz; s.pcache = h->pcache; s.vst = h->shared_grid ? 1 : g.nens;
     s.a = a; s.b = b; s.c = b * dt_full; s.first = d == 0; s.sbits = sbits_state(h, g, dir, nn[dir]); s.labits = labits_for(h, dir);
-    s.seg_only = -1;
+    s.seg_only = -1; s.general_2d = h->general_2d;
     TracerSweepArgs t;
     t.qin = qin; t.mflux = h->mflux[dir]; t.tflux = h->tflux[dir]; t.vtab = h->vtab; t.vst = s.vst; t.sbits = sbits_for(h, nn[dir]); t.labits = s.labits;
     t.seg_only = -1;
@@ -1197,6 +1198,7 @@ int awfl_create(const awfl_config *cfg, awfl_handle **out) {
   ALLOC(h->trptr_out_d, sizeof(double *) * nt);
   h->stage_fields = nullptr; h->stage_out = nullptr; h->tmp_state = nullptr; h->halo_pressure = nullptr;
   { const char *ev = getenv("AWFL_FUSED_FCT"); h->fused_fct = !(ev && atoi(ev) == 0); }
+  { const char *ev = getenv("AWFL_GENERAL_2D"); h->general_2d = ev && atoi(ev) == 1; }
   h->s_in = nullptr; h->s_out = nullptr; h->host_last_ncycles = 0; h->host_mispredictions = 0;
   {
     // member slabs of awfl_time_step_host: chosen from the grid by default (host_slab_count); AWFL_HOST_SLABS overrides

@@ -18,8 +18,15 @@
 
 namespace awfl {
 
-// Ring fields in marching order: the acoustic pair first, then the four advected quantities, then density.
-enum { RF_M = 0, RF_P, RF_U, RF_V, RF_W, RF_T, RF_R, RF_COUNT };
+// Ring fields in marching order: the acoustic pair first, then the advected quantities, then density. The RECONSTRUCTED
+// fields are contiguous from 0. In a 2-D run (S2D) v is not one of them: the reference zeroes the v tendency there
+// (Dycore.h:565), so the flux of v -- one of the six reconstructions per cell and direction -- never reaches a result.
+// v then sits behind theta, only for the stage combination of its round-tripped value.
+enum { RF_COUNT = 7 };
+template <bool S2D> struct RingF {
+  static constexpr int M = 0, P = 1, U = 2, V = S2D ? 5 : 3, W = S2D ? 3 : 4, T = S2D ? 4 : 5, R = 6;
+  static constexpr int NVAR = S2D ? 5 : 6;                   // reconstructed: M, P, U, [V,] W, T
+};
 
 #ifndef AWFL_MINB5
 #define AWFL_MINB5 12
@@ -180,9 +187,13 @@ template <int ORD> struct MatSel<ORD, 3> {
 #define AWFL_MAXNREG_H 168
 #endif
 #define AWFL_STATE_BOUNDS __launch_bounds__(MT) __maxnreg__(ORD == 3 ? 128 : (ORD == 5 ? (DIR == 2 ? AWFL_MAXNREG_Z : AWFL_MAXNREG_H) : 255))
-template <int ORD, int DIR, int MODE, int VT>
+template <int ORD, int DIR, int MODE, int VT, bool S2D>
 __global__ void AWFL_STATE_BOUNDS
 k_march_state(const Geom g, const Phys ph, const SweepArgs a) {
+  using F = RingF<S2D>;
+  constexpr int NVAR = F::NVAR;
+  // 2-D: v is only needed where the stage is combined (its round-tripped value), not by a sweep that accumulates tendencies
+  constexpr bool NEED_V = !(S2D && MODE == 0);
   constexpr int HS = (ORD + 1) / 2;
   constexpr double cs = 350.0;             // Dycore.h:335
   constexpr double rcs = 1.0 / 350.0;
@@ -221,7 +232,8 @@ k_march_state(const Geom g, const Phys ph, const SweepArgs a) {
   const long pdelta = a.pcache - q;                                   // the pressure of a cell sits at the same offset in its own field
   auto fetch_next = [&]() -> Raw {
     Raw x;
-    x.r = __ldg(qp); x.ru = __ldg(qp + nc); x.rv = __ldg(qp + 2 * nc); x.rw = __ldg(qp + 3 * nc);
+    x.r = __ldg(qp); x.ru = __ldg(qp + nc); x.rw = __ldg(qp + 3 * nc);
+    x.rv = NEED_V ? __ldg(qp + 2 * nc) : 0.0;
     x.rt = __ldg(qp + 4 * nc);
     // the pressure C0 (rho theta)^gamma of a cell is the same in every direction of a stage: the x march (always the
     // first sweep) computes it, the other marches read it back -- one x^gamma (~160 instructions) per cell and stage
@@ -260,13 +272,13 @@ k_march_state(const Geom g, const Phys ph, const SweepArgs a) {
       p = (p / A) * rg * X;            // C0 (rho_g theta0)^gamma, Dycore.h:691-694
       r = rg; w = 0.0; m = 0.0;
     }
-    rb[(RF_M * ORD) * MT + so] = m;
-    rb[(RF_P * ORD) * MT + so] = p;
-    rb[(RF_U * ORD) * MT + so] = x.ru * rinv;
-    rb[(RF_V * ORD) * MT + so] = x.rv * rinv;
-    rb[(RF_W * ORD) * MT + so] = w;
-    rb[(RF_T * ORD) * MT + so] = x.rt * rinv;
-    rb[(RF_R * ORD) * MT + so] = r;
+    rb[(F::M * ORD) * MT + so] = m;
+    rb[(F::P * ORD) * MT + so] = p;
+    rb[(F::U * ORD) * MT + so] = x.ru * rinv;
+    if (NEED_V) rb[(F::V * ORD) * MT + so] = x.rv * rinv;
+    rb[(F::W * ORD) * MT + so] = w;
+    rb[(F::T * ORD) * MT + so] = x.rt * rinv;
+    rb[(F::R * ORD) * MT + so] = r;
   };
 
   int head = 0;                       // ring slot of the oldest of the ORD most recent cells
@@ -297,7 +309,7 @@ k_march_state(const Geom g, const Phys ph, const SweepArgs a) {
     const bool flux_on = c >= it.c0;           // interface c belongs to this segment
     const bool wall = (DIR == 2) && (c == 0 || c == n);   // Dycore.h:477,482,496
     const int so = ring_slot<ORD>(head, HS - 2);   // ring slot of cell c-1
-    const double rho = (upd_on && MODE != 0) ? rb[(RF_R * ORD) * MT + so] : 0.0;
+    const double rho = (upd_on && MODE != 0) ? rb[(F::R * ORD) * MT + so] : 0.0;
     double rn = 0.0, pp = 0.0;
     bool up = false;
     // Read-modify-write operands of cell c-1 (partial tendency, step-start state) arrive by asynchronous copies. Where the
@@ -312,30 +324,88 @@ k_march_state(const Geom g, const Phys ph, const SweepArgs a) {
     // and the shared-memory slots: a quarter of the z march's non-FP64 instructions, profiles/r02d_state_z_line_mix.txt.)
     const double *pf_t = a.tend + idx, *pf_q = a.qbase + idx;   // operands still to be staged: partial tendency, step-start state
     double *pf_s = stg;                                        // ... and where they are staged: (tend, base) pairs
+    // 2-D: the step-start v of cell c-1 for its stage combination (its field is skipped by the cursors); loaded here, used last
+    double qb_v = 0.0;
+    if (S2D && ld_q) qb_v = a.qbase[idV * nc + idx];           // plain load: qout may alias qbase, read before the write below
+    // the reconstructed variables go NV at a time; where NV does not divide their number (2-D) a shorter last group follows
+    constexpr int VFULL = (NVAR / NV) * NV, NTAIL = NVAR - VFULL;
+    // state field behind reconstructed variable v >= 1: rho, u, [v,] w, theta -- in 2-D the field cursors step over v
     auto start_copies = [&](int g0) {
 #pragma unroll
       for (int i = 0; i < NV; i++) {
-        if (g0 + i > 0) {
+        const int v = g0 + i;
+        if (v > 0 && (NTAIL == 0 || v < NVAR)) {
           if (ld_t) cp_async8(pf_s, pf_t);
           if (ld_q) cp_async8(pf_s + MT, pf_q);   // qout may alias qbase: read before the write below
-          pf_s += 2 * MT; pf_t += nc; pf_q += nc;
+          pf_s += 2 * MT;
+          if (S2D && v == 2) { pf_t += 2 * nc; pf_q += 2 * nc; } else { pf_t += nc; pf_q += nc; }
         }
       }
     };
     if (PRE_ALL && (ld_t || ld_q)) {
 #pragma unroll
-      for (int g0 = 0; g0 < 6; g0 += NV) { start_copies(g0); cp_async_commit(); }
+      for (int g0 = 0; g0 < NVAR; g0 += NV) { start_copies(g0); cp_async_commit(); }
     }
     if (!PRE_ALL && (ld_t || ld_q)) { start_copies(0); cp_async_commit(); }
-    double *po = (MODE == 0 ? a.tend : a.qout) + idx;           // where variable l of cell c-1 goes
+    double *po = (MODE == 0 ? a.tend : a.qout) + idx;           // where the state field of the current variable goes (cell c-1)
     const double *sg = stg;                                     // its staged operands
-    double *fl = fpv;                                           // flux of variable l through the previous interface
-    double *fe = fpv + (NS - 1) * MT;                           // right-edge value of variable l (l >= 1) in the previous cell
-    const double *rl = rb + ((RF_U - 1) * ORD) * MT + so;       // primitive variable l (l >= 1) of cell c-1 in the ring
-    // reconstructed quantities in ring order: rho*u_n, p (acoustic pair), then u, v, w, theta -- NV at a time
+    double *fl = fpv;                                           // its flux through the previous interface
+    double *fe = fpv + (NS - 1) * MT;                           // its right-edge value in the previous cell (advected variables)
+    const double *rl = rb + ((F::U - 1) * ORD) * MT + so;       // its primitive value of cell c-1 in the ring (advected variables)
+    // one reconstructed variable: v = 0 rho*u_n, 1 p (the acoustic pair closes interface c), then the advected u, [v,] w, theta
+    auto handle = [&](int v, double E, double O) {
+      if (v == 0) { mRs = E - O; mLns = E + O; return; }
+      // this variable's cursors; the shared ones move on to the next variable
+      double *const po_l = po, *const fl_l = fl, *const fe_l = fe;
+      const double *const sg_l = sg, *const rl_l = rl;
+      po += (S2D && v == 2) ? 2 * nc : nc;
+      sg += 2 * MT; fl += MT; fe += MT; rl += ORD * MT;
+      int l;
+      double Fx;
+      if (v == 1) {
+        // interface c: characteristic upwinding, Dycore.h:361-365
+        const double pR = E - O;
+        double mR = mRs;
+        if (wall) { mL = 0.0; mR = 0.0; }
+        const double w1 = 0.5 * (pR - cs * mR);
+        const double w2 = 0.5 * (pL + cs * mL);
+        pp = w1 + w2;
+        rn = wall ? 0.0 : (w2 - w1) * rcs;
+        up = rn > 0.0;               // Dycore.h:368: the upwind cell is c-1 when the mass flux is positive
+        mL = mLns; pL = E + O;
+        // interface mass flux for the tracer march (x,y: n entries, seam stored at 0; z: n+1 entries)
+        if (flux_on && (c < it.c1 || (DIR == 2 && c == n))) a.mflux[it.base + (long)c * sd] = rn;
+        l = idR; Fx = rn;
+      } else {
+        l = (S2D && v >= 3) ? v : v - 1;                        // idU..idT
+        Fx = rn * (up ? fe_l[0] : E - O);
+        fe_l[0] = E + O;
+        if (l == NORMAL) Fx += pp;
+      }
+      if (!flux_on) return;
+      if (upd_on) {
+        const double div = (Fx - fl_l[0]) * rdd;
+        double T = (ld_t ? sg_l[0] : 0.0) - div;
+        if (MODE == 0) po_l[0] = T;
+        else {
+          if (l == idW) T = fma(-gv, rho, T);                 // Dycore.h:560
+          if (!S2D && l == idV && g.sim2d) T = 0.0;           // Dycore.h:565 (a 2-D run on the general kernel)
+          if (MODE == 2) po_l[0] = T;
+          else {
+            // round-tripped stage input (x/rho)*rho, Dycore.h:316-319 + :527-530
+            const double rt = l == idR ? rho : rl_l[0] * rho;
+            const double o = fma(a.a, ld_q ? sg_l[MT] : 0.0, a.b * rt);
+            po_l[0] = fma(a.c, T, o);
+          }
+        }
+      }
+      fl_l[0] = Fx;
+    };
+    // reconstructed quantities in ring order, NV at a time: their reconstructions together (shared table loads), then each
+    // variable's fluxes / update
 #pragma unroll(V0_UNROLL)
-    for (int v0 = 0; v0 < 6; v0 += NV) {
-      if (!PRE_ALL && (ld_t || ld_q)) { if (v0 + NV < 6) start_copies(v0 + NV); cp_async_commit(); }   // one group ahead
+    for (int v0 = 0; v0 < VFULL; v0 += NV) {
+      if (!PRE_ALL && (ld_t || ld_q)) { if (v0 + NV < NVAR) start_copies(v0 + NV); cp_async_commit(); }   // one group ahead
       // vertical marches on a shared grid: inlined (uniform per-level table loads are not hoisted out of the cell loop, and
       // without the call the ~100 argument / return moves per cell go away: z march 7.80 -> 7.33 ms). Horizontal marches
       // and member-dependent grids keep the real call (see weno_ring; inlined they spill: measured 7.11 vs 6.78 ms in x,
@@ -344,59 +414,26 @@ k_march_state(const Geom g, const Phys ph, const SweepArgs a) {
       if constexpr (VT == 1 || VT == 3) eo = weno_ring_inl<ORD, NV>(rb + (v0 * ORD) * MT, head, mat);
       else eo = weno_ring<ORD, NV>(rb + (v0 * ORD) * MT, head, mat);
       if (ld_t || ld_q) {
-        if (PRE_ALL) cp_async_wait_left((6 - NV - v0) / NV);     // the later groups may still be in flight
+        if (PRE_ALL) cp_async_wait_left((NVAR - 1 - v0) / NV);   // the later groups may still be in flight
         else cp_async_wait_left(1);                              // all but the group just started
       }
 #pragma unroll
-      for (int i = 0; i < NV; i++) {
-        const int v = v0 + i;
-        const double E = eo.E[i], O = eo.O[i];
-        if (v == 0) { mRs = E - O; mLns = E + O; continue; }
-        // this variable's cursors; the shared ones move on to the next variable
-        double *const po_l = po, *const fl_l = fl, *const fe_l = fe;
-        const double *const sg_l = sg, *const rl_l = rl;
-        po += nc; sg += 2 * MT; fl += MT; fe += MT; rl += ORD * MT;
-        int l;
-        double F;
-        if (v == 1) {
-          // interface c: characteristic upwinding, Dycore.h:361-365
-          const double pR = E - O;
-          double mR = mRs;
-          if (wall) { mL = 0.0; mR = 0.0; }
-          const double w1 = 0.5 * (pR - cs * mR);
-          const double w2 = 0.5 * (pL + cs * mL);
-          pp = w1 + w2;
-          rn = wall ? 0.0 : (w2 - w1) * rcs;
-          up = rn > 0.0;               // Dycore.h:368: the upwind cell is c-1 when the mass flux is positive
-          mL = mLns; pL = E + O;
-          // interface mass flux for the tracer march (x,y: n entries, seam stored at 0; z: n+1 entries)
-          if (flux_on && (c < it.c1 || (DIR == 2 && c == n))) a.mflux[it.base + (long)c * sd] = rn;
-          l = idR; F = rn;
-        } else {
-          l = v - 1;                   // idU..idT
-          F = rn * (up ? fe_l[0] : E - O);
-          fe_l[0] = E + O;
-          if (l == NORMAL) F += pp;
-        }
-        if (!flux_on) continue;
-        if (upd_on) {
-          const double div = (F - fl_l[0]) * rdd;
-          double T = (ld_t ? sg_l[0] : 0.0) - div;
-          if (MODE == 0) po_l[0] = T;
-          else {
-            if (l == idW) T = fma(-gv, rho, T);                 // Dycore.h:560
-            if (l == idV && g.sim2d) T = 0.0;                   // Dycore.h:565
-            if (MODE == 2) po_l[0] = T;
-            else {
-              // round-tripped stage input (x/rho)*rho, Dycore.h:316-319 + :527-530
-              const double rt = l == idR ? rho : rl_l[0] * rho;
-              const double o = fma(a.a, ld_q ? sg_l[MT] : 0.0, a.b * rt);
-              po_l[0] = fma(a.c, T, o);
-            }
-          }
-        }
-        fl_l[0] = F;
-      }
+      for (int i = 0; i < NV; i++) handle(v0 + i, eo.E[i], eo.O[i]);
+    }
+    if constexpr (NTAIL > 0) {
+      // 2-D: the shorter last group, always through the real call (a second inlined reconstruction next to the loop's spills
+      // 0.8-4.7 KB in the vertical marches)
+      if (!PRE_ALL && (ld_t || ld_q)) cp_async_commit();
+      const EOn<NTAIL> eo = weno_ring<ORD, NTAIL>(rb + (VFULL * ORD) * MT, head, mat);
+      if (ld_t || ld_q) cp_async_wait_left(0);
+#pragma unroll
+      for (int i = 0; i < NTAIL; i++) handle(VFULL + i, eo.E[i], eo.O[i]);
+    }
+    if (S2D && upd_on && MODE != 0) {
+      // v of cell c-1 in a 2-D run: tendency 0 (Dycore.h:565), i.e. the stage combination of its round-tripped value
+      double *const pv = a.qout + idV * nc + idx;
+      if (MODE == 2) pv[0] = 0.0;
+      else pv[0] = fma(a.a, qb_v, a.b * (rb[(F::V * ORD) * MT + so] * rho));
     }
   }
 }

@@ -37,17 +37,26 @@ template <int ORD>
 void OrdLaunch<ORD>::march_state(cudaStream_t s, const Geom &g, const Phys &ph, const SweepArgs &a, int dir, int mode, int vt) {
   const dim3 blocks = march_grid(g, dir, a.sbits, a.labits, 1, 1);
   constexpr size_t B = MarchCfg<ORD>::SMEM_STATE;
-  // x and y sweeps only ever accumulate (MODE 0); the z sweep is always the last of a stage (MODE 1 or 2)
-  if (dir == 0) AWFL_LAUNCH_MARCH((k_march_state<ORD, 0, 0, 0>), B, g, ph, a);
-  else if (dir == 1) AWFL_LAUNCH_MARCH((k_march_state<ORD, 1, 0, 0>), B, g, ph, a);
+  // x and y sweeps only ever accumulate (MODE 0); the z sweep is always the last of a stage (MODE 1 or 2). A 2-D run
+  // (ny == 1, no y sweep) takes the kernels that leave the reconstruction of v out (RingF in awfl_march.cuh) unless the
+  // handle asks for the general ones
+  const bool s2d = g.sim2d && !a.general_2d;
+#define AWFL_STATE_CASE(D, M, V)                                                       \
+  do {                                                                                 \
+    if (s2d) AWFL_LAUNCH_MARCH((k_march_state<ORD, D, M, V, true>), B, g, ph, a);      \
+    else AWFL_LAUNCH_MARCH((k_march_state<ORD, D, M, V, false>), B, g, ph, a);         \
+  } while (0)
+  if (dir == 0) AWFL_STATE_CASE(0, 0, 0);
+  else if (dir == 1) AWFL_LAUNCH_MARCH((k_march_state<ORD, 1, 0, 0, false>), B, g, ph, a);
   else if (mode == 1) {
-    if (vt == 1) AWFL_LAUNCH_MARCH((k_march_state<ORD, 2, 1, 1>), B, g, ph, a);
-    else if (vt == 3) AWFL_LAUNCH_MARCH((k_march_state<ORD, 2, 1, 3>), B, g, ph, a);
-    else AWFL_LAUNCH_MARCH((k_march_state<ORD, 2, 1, 2>), B, g, ph, a);
+    if (vt == 1) AWFL_STATE_CASE(2, 1, 1);
+    else if (vt == 3) AWFL_STATE_CASE(2, 1, 3);
+    else AWFL_STATE_CASE(2, 1, 2);
   } else {
-    if (vt == 1) AWFL_LAUNCH_MARCH((k_march_state<ORD, 2, 2, 1>), B, g, ph, a);
-    else AWFL_LAUNCH_MARCH((k_march_state<ORD, 2, 2, 2>), B, g, ph, a);
+    if (vt == 1) AWFL_STATE_CASE(2, 2, 1);
+    else AWFL_STATE_CASE(2, 2, 2);
   }
+#undef AWFL_STATE_CASE
 }
 
 template <int ORD>
@@ -64,13 +73,19 @@ void OrdLaunch<ORD>::march_tracer(cudaStream_t s, const Geom &g, const TracerSwe
 template <int ORD>
 void OrdLaunch<ORD>::configure() {
   constexpr size_t BS = MarchCfg<ORD>::SMEM_STATE, BT = MarchCfg<ORD>::SMEM_TRACER;
-  configure_march(k_march_state<ORD, 0, 0, 0>, BS);
-  configure_march(k_march_state<ORD, 1, 0, 0>, BS);
-  configure_march(k_march_state<ORD, 2, 1, 1>, BS);
-  configure_march(k_march_state<ORD, 2, 1, 2>, BS);
-  configure_march(k_march_state<ORD, 2, 1, 3>, BS);
-  configure_march(k_march_state<ORD, 2, 2, 1>, BS);
-  configure_march(k_march_state<ORD, 2, 2, 2>, BS);
+  configure_march(k_march_state<ORD, 0, 0, 0, false>, BS);
+  configure_march(k_march_state<ORD, 0, 0, 0, true>, BS);
+  configure_march(k_march_state<ORD, 1, 0, 0, false>, BS);
+  configure_march(k_march_state<ORD, 2, 1, 1, false>, BS);
+  configure_march(k_march_state<ORD, 2, 1, 2, false>, BS);
+  configure_march(k_march_state<ORD, 2, 1, 3, false>, BS);
+  configure_march(k_march_state<ORD, 2, 2, 1, false>, BS);
+  configure_march(k_march_state<ORD, 2, 2, 2, false>, BS);
+  configure_march(k_march_state<ORD, 2, 1, 1, true>, BS);
+  configure_march(k_march_state<ORD, 2, 1, 2, true>, BS);
+  configure_march(k_march_state<ORD, 2, 1, 3, true>, BS);
+  configure_march(k_march_state<ORD, 2, 2, 1, true>, BS);
+  configure_march(k_march_state<ORD, 2, 2, 2, true>, BS);
   configure_march(k_march_tracer<ORD, 0, 0>, BT);
   configure_march(k_march_tracer<ORD, 1, 0>, BT);
   configure_march(k_march_tracer<ORD, 2, 1>, BT);

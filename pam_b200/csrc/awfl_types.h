@@ -38,6 +38,7 @@ struct SweepArgs {
   int first;              // 1: this is the first sweep of the stage (tend is written, not accumulated)
   int sbits, labits;      // grid encoding (decode_item): 2^sbits segments per line, labits bits for the first line index
   int seg_only;           // >= 0: only this segment of every line works, the other blocks leave at once (paged vertical tables)
+  int general_2d;         // 2-D run on the general kernels, which reconstruct v too (AWFL_GENERAL_2D=1 at create time: A/B and agreement tests)
 };
 
 // Tracer march arguments (k_march_tracer)

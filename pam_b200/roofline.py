@@ -42,9 +42,13 @@ def recon_flops_hand_formula(ord):
 
 
 def flops_per_cell_stage(ord, nt, ndir):
-    """Reference flops per cell per Runge-Kutta stage: reconstructions + everything else (products, characteristics,
-    divergence, FCT, update, one pow counted as 1)."""
-    per_dir = (8 + nt) * recon_flops(ord)[0] + 2 * ord + 12 + 2 * (4 + nt) + 3 * (5 + nt)
+    """Reference flops per cell per Runge-Kutta stage that reach a result: reconstructions + everything else (products,
+    characteristics, divergence, FCT, update, one pow counted as 1). A 2-D run (ndir == 2) has 3 advective reconstructions
+    per direction, not 4: the reference reconstructs v and forms its flux there too, then zeroes the tendency
+    (Dycore.h:565) -- work that no output depends on is not counted as algorithmic (it was until r02D, when the 2-D marches
+    stopped executing it; counted, the state marches would read 1.00 of the FP64 peak)."""
+    adv = 3 if ndir == 2 else 4
+    per_dir = (4 + adv + nt) * recon_flops(ord)[0] + 2 * ord + 12 + 2 * (adv + nt) + 3 * (1 + adv + nt)
     other = 5 + 4 + nt + (5 + nt) * 5 + nt * 30
     return ndir * per_dir + other
 
@@ -53,10 +57,12 @@ def flops_per_cell_update(ord, nt, ndir):
     return 3 * flops_per_cell_stage(ord, nt, ndir)
 
 
-def state_sweep_flops_per_cell(ord):
+def state_sweep_flops_per_cell(ord, sim2d=False):
     """Reference flops of the part of the flux kernel the state sweep replaces, per cell and direction: 4 acoustic + 4
-    advective reconstructions, stencil products, characteristics, 5 fluxes, divergence."""
-    return 8 * recon_flops(ord)[0] + 2 * ord + 12 + 8 + 15
+    advective reconstructions (3 in a 2-D run, see flops_per_cell_stage), stencil products, characteristics, the fluxes,
+    divergence."""
+    adv = 3 if sim2d else 4
+    return (4 + adv) * recon_flops(ord)[0] + 2 * ord + 12 + 2 * adv + 3 * (1 + adv)
 
 
 def bytes_per_cell_update(nt):

@@ -105,6 +105,10 @@ def test_roofline_counts_are_frozen():
         assert abs(roofline.recon_flops_hand_formula(o)[0] / roofline.recon_flops(o)[0] - 1.0) < 0.021
     assert roofline.bytes_per_cell_update(1) == 384 and roofline.bytes_per_cell_update(10) == 960
     assert roofline.state_sweep_flops_per_cell(5) == 8 * 295 + 10 + 12 + 8 + 15
+    # 2-D: the reconstruction and flux of v, which the reference computes and discards (Dycore.h:565), is not algorithmic work
+    assert roofline.state_sweep_flops_per_cell(5, sim2d=True) == 7 * 295 + 10 + 12 + 6 + 12
+    assert roofline.flops_per_cell_stage(5, 1, 3) == 3 * (9 * 295 + 10 + 12 + 10 + 18) + 5 + 4 + 1 + 30 + 30
+    assert roofline.flops_per_cell_stage(5, 1, 2) == 2 * (8 * 295 + 10 + 12 + 8 + 15) + 5 + 4 + 1 + 30 + 30
 
 
 def test_instrumented_flop_count_reproduces_the_frozen_numbers(tmp_path):

@@ -128,6 +128,26 @@ int awfl_compute_tendencies_haloed(awfl_handle *h, double *state, double *state_
  * (the reference returns a device real2d). */
 int awfl_compute_mass_dynamics(awfl_handle *h, const double *state, const double *tracers, double *out_device);
 
+/* awfl_compute_mass_dynamics without a handle and WITHOUT ANY ALLOCATION. No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving
+ * loops, harnesses that forbid it). Calls no cudaMalloc / cudaFree / allocating library routine and does not synchronise:
+ * two kernels go to `stream` (a cudaStream_t, NULL = the default stream).
+ *   state (5,nz+2hs,ny+2hs,nx+2hs,nens), tracers (num_tracers,...): DEVICE haloed arrays as above, hs = (ord+1)/2;
+ *   dz (nz,nens): DEVICE cell heights; out_device (num_tracers+2,nens): DEVICE result, same values as
+ *   awfl_compute_mass_dynamics (same kernels, same summation order).
+ * The de-haloed copy of the fields goes to a static device array of AWFL_NOALLOC_MAX_DOUBLES doubles (16 MiB) that every
+ * GPU which loads the library holds until the process exits: (5 + num_tracers) * nz * ny * nx * nens beyond that is
+ * rejected (return 1, text in awfl_last_error(NULL)). The arrays must live on the CURRENT device. All calls on a device
+ * share the static array: calls that overlap on the GPU (different streams without a dependency) race; calls on one
+ * stream, or otherwise ordered, do not. Nothing in it has to start at zero.
+ * awfl_noalloc_setup() resolves the array's device address for the current device (done by the first call otherwise):
+ * call it once per device before a graph capture begins. */
+#define AWFL_NOALLOC_MAX_DOUBLES (1ul << 21)
+int awfl_noalloc_setup(void);
+unsigned long awfl_noalloc_max_doubles(void);
+int awfl_compute_mass_dynamics_noalloc(int nz, int ny, int nx, int nens, int num_tracers, int ord, const double *state,
+                                       const double *tracers, const double *dz, double *out_device, void *stream);
+
 /* Dycore::init_supercell (Dycore.h:1096-1276): the supercell sounding as interior values of state / tracers.
  * zint: DEVICE "vertical_interface_height" (nz+1,nens). Init-time call: allocates scratch and synchronises. */
 int awfl_init_supercell(awfl_handle *h, double *state, double *tracers, const double *zint);

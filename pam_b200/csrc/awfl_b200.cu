@@ -1827,3 +1827,85 @@ int awfl_measure_fp64_peak(awfl_handle *h, int iters, double *tflops) {
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------------------------------
+// An entry point that allocates nothing (no counterpart in the reference; added for
+// callers that cannot call cudaMalloc: code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+// awfl_compute_mass_dynamics gathers the interior of the haloed arrays into the handle's workspace and sums it there; this
+// variant needs no handle, and its workspace is the file-scope device array below. Every GPU that loads the library holds
+// the array (AWFL_NOALLOC_MAX_DOUBLES * 8 bytes = 16 MiB) until the process exits.
+//   * In host code `g_noalloc_scratch` is a host-side stand-in, NOT a device address: the kernels are given the address
+//     cudaGetSymbolAddress returns, fetched once per device with that device current (noalloc_scratch below).
+//   * Every call on a device shares the array, which keeps the previous call's contents. Nothing has to start at zero:
+//     the gather writes every element the sum reads before it reads it (same stream). Calls that overlap on the GPU
+//     (different streams, no dependency between them) race on the array.
+// ---------------------------------------------------------------------------------------------------------------
+static __device__ __align__(256) double g_noalloc_scratch[AWFL_NOALLOC_MAX_DOUBLES];
+namespace {
+constexpr int NOALLOC_MAX_DEVICES = 64;
+std::mutex g_noalloc_mu;
+double *g_noalloc_ptr[NOALLOC_MAX_DEVICES] = {};   // device address of g_noalloc_scratch, per device
+// device address of the array on the CURRENT device (set-up on the first call there), or NULL with g_create_err set
+double *noalloc_scratch() {
+  int dev = -1;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) { g_create_err = std::string("no-alloc entry point: cudaGetDevice: ") + cudaGetErrorString(e); return nullptr; }
+  if (dev < 0 || dev >= NOALLOC_MAX_DEVICES) { g_create_err = "no-alloc entry point: device ordinal beyond 63"; return nullptr; }
+  std::lock_guard<std::mutex> lk(g_noalloc_mu);
+  if (!g_noalloc_ptr[dev]) {
+    double *p = nullptr;
+    e = cudaGetSymbolAddress((void **)&p, g_noalloc_scratch);
+    if (e != cudaSuccess || !p) {
+      g_create_err = std::string("no-alloc entry point: cudaGetSymbolAddress: ") + cudaGetErrorString(e);
+      return nullptr;
+    }
+    g_noalloc_ptr[dev] = p;
+  }
+  return g_noalloc_ptr[dev];
+}
+}  // namespace
+
+extern "C" {
+
+unsigned long awfl_noalloc_max_doubles(void) { return (unsigned long)AWFL_NOALLOC_MAX_DOUBLES; }
+
+int awfl_noalloc_setup(void) { return noalloc_scratch() ? 0 : 1; }
+
+int awfl_compute_mass_dynamics_noalloc(int nz, int ny, int nx, int nens, int num_tracers, int ord, const double *state,
+                                       const double *tracers, const double *dz, double *out_device, void *stream) {
+  if (nz < 1 || ny < 1 || nx < 1 || nens < 1 || num_tracers < 0 || ord < 1 || !(ord & 1)) {
+    g_create_err = "awfl_compute_mass_dynamics_noalloc: bad dimensions or order";
+    return 1;
+  }
+  if (!state || !dz || !out_device || (num_tracers > 0 && !tracers)) {
+    g_create_err = "awfl_compute_mass_dynamics_noalloc: null array";
+    return 1;
+  }
+  const double need = (double)nz * ny * nx * nens * (double)(NS + num_tracers);
+  if (need > (double)AWFL_NOALLOC_MAX_DOUBLES) {
+    char msg[256];
+    snprintf(msg, sizeof msg, "awfl_compute_mass_dynamics_noalloc: (5 + num_tracers) * nz * ny * nx * nens = %.0f doubles exceeds the "
+             "static workspace of %lu doubles (use awfl_compute_mass_dynamics, whose workspace belongs to a handle)", need,
+             (unsigned long)AWFL_NOALLOC_MAX_DOUBLES);
+    g_create_err = msg;
+    return 1;
+  }
+  double *scratch = noalloc_scratch();
+  if (!scratch) return 1;
+  Geom g;
+  g.nz = nz; g.ny = ny; g.nx = nx; g.nens = nens; g.nt = num_tracers;
+  g.sim2d = ny == 1;
+  g.ncell = (long)nz * ny * nx * nens;
+  g.dx = g.dy = 0.0;                    // not used by the two kernels below
+  g.e0 = 0; g.ne = nens;
+  cudaStream_t st = (cudaStream_t)stream;
+  const RowMap rm = row_map(g, 256);
+  k_h_gather<<<row_blocks(g, rm), 256, 0, st>>>(g, rm, halo_dims(g, (ord + 1) / 2), state, tracers, scratch);
+  const long n = (long)(num_tracers + 2) * nens;
+  k_mass<<<(unsigned)((n + 127) / 128), 128, 0, st>>>(g, scratch, dz, out_device);
+  const cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) { g_create_err = std::string("awfl_compute_mass_dynamics_noalloc: launch: ") + cudaGetErrorString(e); return 1; }
+  return 0;
+}
+
+}  // extern "C"

@@ -878,10 +878,20 @@ static int sbits_for(const awfl_handle *h, int n, int seg_len = 0) {
 // are enough of them to fill the GPU (C2: 6.13 -> 6.04 ms in x, 7.12 -> 7.03 ms in z); a member slab of the host-buffer
 // entry point brings few lines and keeps the shorter segments (e2e 1.17 vs 1.27 G with whole lines). The tracer march has
 // no such conversion and prefers the shorter segments either way (1.18 vs 1.08 ms).
-static int sbits_state(const awfl_handle *h, const Geom &g, int dir, int n) {
+static long march_lines(const Geom &g, int dir) {
   const long lines = dir == 0 ? (long)g.nz * g.ny : (dir == 1 ? (long)g.nz * g.nx : (long)g.ny * g.nx);
-  const long warps = lines * ((g.ne + 31) / 32);
-  return sbits_for(h, n, warps >= 4096 ? 2 * h->seg_len : h->seg_len);
+  return lines * ((g.ne + 31) / 32);
+}
+// A launch that brings too few one-warp blocks to occupy the GPU even once (a standalone CRM: BASELINE.json configs[0] has 50
+// lines) is bound by the LATENCY of one warp walking its line: shorter segments, down to 8 cells, until the blocks fill the
+// 148 x 12 slots of one wave. The halo cells a segment recomputes cost nothing there. (C1: 1.09 -> see DESIGN.md 5.)
+static int sbits_fill(int sb, int n, long warps) {
+  while (sb < 4 && (n >> (sb + 1)) >= 8 && (warps << (sb + 1)) <= 148L * 12) sb++;
+  return sb;
+}
+static int sbits_state(const awfl_handle *h, const Geom &g, int dir, int n) {
+  const long warps = march_lines(g, dir);
+  return sbits_fill(sbits_for(h, n, warps >= 4096 ? 2 * h->seg_len : h->seg_len), n, warps);
 }
 static int labits_for(const awfl_handle *h, int dir) {
   const int la = dir == 2 ? h->g.ny : h->g.nz;
@@ -1000,7 +1010,7 @@ static void run_stage(awfl_handle *h, const Geom &g, const double *qin, const do
     s.a = a; s.b = b; s.c = b * dt_full; s.first = d == 0; s.sbits = sbits_state(h, g, dir, nn[dir]); s.labits = labits_for(h, dir);
     s.seg_only = -1; s.general_2d = h->general_2d;
     TracerSweepArgs t;
-    t.qin = qin; t.mflux = h->mflux[dir]; t.tflux = h->tflux[dir]; t.vtab = h->vtab; t.vst = s.vst; t.sbits = sbits_for(h, nn[dir]); t.labits = s.labits;
+    t.qin = qin; t.mflux = h->mflux[dir]; t.tflux = h->tflux[dir]; t.vtab = h->vtab; t.vst = s.vst; t.sbits = sbits_fill(sbits_for(h, nn[dir]), nn[dir], (march_lines(g, dir) + 1) / 2 * g.nt); t.labits = s.labits;
     t.seg_only = -1;
     if (dir == 2 && h->use_cvpage && h->cvpage_ok) {
       // paged vertical table: segment by segment, the state and the tracer march of a page behind its upload (stream order

@@ -336,6 +336,27 @@ def test_2d_marches_without_v_agree_with_the_general_marches(ord, grid, extra, m
         assert rel_l2(out["0"][k], ref[k], fl[k]) <= 2 * TOL_STEP, (k, rel_l2(out["0"][k], ref[k], fl[k]))
 
 
+@pytest.mark.parametrize("ord,ny", [(5, 1), (9, 1), (5, 6), (3, 1)])
+def test_segment_length_does_not_change_a_bit(ord, ny, monkeypatch):
+    """Lines are marched in segments (a block per segment; short ones when a launch would not fill the GPU otherwise, see
+    sbits_fill in awfl_b200.cu). A segment recomputes its halo cells from the same inputs with the same arithmetic: whole
+    lines (AWFL_SEG_LEN=100000), the default and 4-cell segments give identical bits."""
+    case = _case(nz=40, ny=ny, nx=36, nens=40 if ny == 1 else 8, nt=10 if ord == 5 and ny == 1 else 1)
+    out = {}
+    for seg in ("100000", "", "4"):
+        if seg:
+            monkeypatch.setenv("AWFL_SEG_LEN", seg)
+        else:
+            monkeypatch.delenv("AWFL_SEG_LEN", raising=False)
+        c, d = H.make_gpu(case, ord, crm_dt=2.0)
+        d.declare_current_profile_as_hydrostatic(c)
+        d.timeStep(c)
+        out[seg] = H.gpu_fields(c)
+    for seg in ("", "4"):
+        for k in out["100000"]:
+            assert np.array_equal(out["100000"][k], out[seg][k]), (seg, k)
+
+
 def test_errors_are_reported_not_swallowed():
     from pam_b200 import PamCoupler, Dycore
     c = PamCoupler("cuda:0")

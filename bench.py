@@ -303,7 +303,8 @@ def run_workload(w, args, rank, world, dev, nens_global, steps, warmup, do_e2e, 
     launches = d.launch_count() - l0
     upd = allsum(float(ncell) * sum(cyc))
     out = {"value": upd / (ms_total * 1e-3), "ms_per_step": ms_total / steps, "cyc": cyc, "launches": launches, "clocks": clocks,
-           "ncell": ncell, "nloc": nloc, "names": names, "nt": len(case["tracers"]), "parity": parity, "updates_per_step": upd / steps}
+           "ncell": ncell, "nloc": nloc, "names": names, "nt": len(case["tracers"]), "parity": parity, "updates_per_step": upd / steps,
+           "fused_tracer": d.fused_tracer()}
 
     # ---- per-kernel-class profile in a SEPARATE pass (an event pair around every launch perturbs the headline slightly) ----
     if do_profile:
@@ -444,12 +445,15 @@ def main():
         pass
     hbm_peak = peaks.get("hbm_gbs", 6650.0)
     hbm_src = "measured (MEASURED_PEAKS.json)" if "hbm_gbs" in peaks else "fallback (B200_PROFILING.md)"
+    # 2-D: the x / z state march (bit 0 / 1) carries the first tracer; the tracer march of that direction runs for the others
+    fused_bits = r.get("fused_tracer", 0)
+    fused_dom = bool(fused_bits >> (1 if dom.endswith("_z") else 0) & 1) and not dom.endswith("_y")
     if dom.startswith("state_"):
-        fl = roofline.state_sweep_flops_per_cell(w["ord"], sim2d=w["ny"] == 1) * ncell
-        by = roofline.state_sweep_bytes_per_cell(last=dom == "state_z") * ncell
+        fl = roofline.state_sweep_flops_per_cell(w["ord"], sim2d=w["ny"] == 1, fused_tracer=fused_dom) * ncell
+        by = roofline.state_sweep_bytes_per_cell(last=dom == "state_z", fused_tracer=fused_dom) * ncell
     elif dom.startswith("tracer_") and dom != "tracer_upd":
-        fl = (roofline.recon_flops(w["ord"])[0] + 4) * ncell * nt
-        by = 8 * 4 * ncell * nt
+        fl = roofline.tracer_sweep_flops_per_cell(w["ord"]) * ncell * (nt - (1 if fused_dom else 0))
+        by = 8 * 4 * ncell * (nt - (1 if fused_dom else 0))
     elif dom == "tracer_upd" and w["ny"] == 1:
         fl, by = 60.0 * ncell * nt, 8 * 5 * ncell * nt       # fused 2-D FCT + update: reads 2 fluxes + 2 states, writes 1 state
     else:
@@ -481,7 +485,10 @@ def main():
                     "instrumented count of tools/count_flops.py), launch time averaged over all launches of the class in a separate "
                     "profiling pass; `traffic` and `hbm.bytes_per_launch` describe a stage-2/3 launch of the class. In a 2-D workload the "
                     "state marches leave out the reconstruction of v, whose flux the reference computes and then discards "
-                    "(Dycore.h:565): those flops are NOT counted in `achieved` (7 reconstructions per cell and direction, not 8)"}
+                    "(Dycore.h:565): those flops are NOT counted in `achieved` (7 reconstructions per cell and direction, not 8); "
+                    "where `fused_tracer` says so the state march also carries the first tracer (its reconstruction and flux are "
+                    "counted in the march that executes them)",
+            "fused_tracer": fused_bits}
     ms_total = r["ms_per_step"] * args.steps
     step_fl = roofline.flops_per_cell_update(w["ord"], w["nt"], ndir) * float(ncell) * sum(cyc)
     step_by = roofline.bytes_per_cell_update(w["nt"]) * float(ncell) * sum(cyc)

@@ -205,6 +205,12 @@ int awfl_reconstruct(awfl_handle *h, const double *stencils, int n, int ind, int
  * levels each segment reads; needs the bank for itself). Results do not depend on it (same arithmetic). */
 int awfl_table_home(const awfl_handle *h);
 
+/* Diagnostic: which state marches of this handle carry the first tracer (2-D runs: its flux, the tracer part of
+ * Dycore.h:381-385 / :513-517, then comes out of the state march and the tracer march runs for the other tracers only).
+ * Bit 0 = x march, bit 1 = z march; 0 for 3-D handles and handles without tracers. Environment AWFL_FUSED_TRACER at create
+ * time overrides the per-order default. */
+int awfl_fused_tracer(const awfl_handle *h);
+
 /* Debug aid: fills every scratch buffer of the handle with NaN bit patterns (on the handle's stream). A later call that
  * read scratch memory before writing it returns NaN -- the check compute-sanitizer's initcheck would make. */
 int awfl_poison_workspace(awfl_handle *h);

@@ -37,7 +37,7 @@ EXPORTS = ("awfl_create", "awfl_destroy", "awfl_last_error", "awfl_dycore_name",
            "awfl_current_device", "awfl_device_alloc", "awfl_device_free", "awfl_set_host_slabs", "awfl_host_slabs", "awfl_host_mispredictions", "awfl_init_idealized",
            "awfl_table_home", "awfl_convert_coupler_to_dynamics", "awfl_convert_dynamics_to_coupler", "awfl_halo_exchange",
            "awfl_compute_tendencies_haloed", "awfl_compute_mass_dynamics", "awfl_init_supercell", "awfl_poison_workspace",
-           "awfl_noalloc_setup", "awfl_noalloc_max_doubles", "awfl_compute_mass_dynamics_noalloc")
+           "awfl_noalloc_setup", "awfl_noalloc_max_doubles", "awfl_compute_mass_dynamics_noalloc", "awfl_fused_tracer")
 
 KERNEL_CLASSES = ("in", "out", "state_x", "state_y", "state_z", "tracer_x", "tracer_y", "tracer_z", "fct", "tracer_upd", "other")
 
@@ -92,6 +92,7 @@ def load():
     lib.awfl_halo_exchange.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
     lib.awfl_compute_tendencies_haloed.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_double]
     lib.awfl_compute_mass_dynamics.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.awfl_fused_tracer.argtypes = [C.c_void_p]
     lib.awfl_noalloc_setup.argtypes = []
     lib.awfl_noalloc_max_doubles.argtypes = []
     lib.awfl_noalloc_max_doubles.restype = C.c_ulong

@@ -28,6 +28,9 @@
 #include "../../include/awfl_b200.h"
 #include "awfl_tables.h"
 #include "awfl_types.h"
+#ifndef AWFL_FUSED_TRACER_Z_MAX_ORD
+#define AWFL_FUSED_TRACER_Z_MAX_ORD 7
+#endif
 
 #ifndef AWFL_FCT_STRIP
 #define AWFL_FCT_STRIP 4
@@ -665,6 +668,7 @@ struct awfl_handle {
   double *stage_fields;  // staging buffer for the host-buffer entry point (5+nt fields)
   int host_last_ncycles;      // sub-cycle count derived by the previous awfl_time_step_host (0 = none yet): the prediction
   long host_mispredictions;   // calls whose prediction was wrong and were redone un-overlapped
+  int fused_tracer;      // 2-D: the first tracer is reconstructed by the state march of x (bit 0) / z (bit 1) instead of the tracer march (AWFL_FUSED_TRACER)
   bool general_2d;       // 2-D on the general state marches (AWFL_GENERAL_2D=1; see SweepArgs::general_2d)
   bool fused_fct;        // 2-D: fused FCT + tracer update kernel (AWFL_FUSED_FCT=0 selects the two-kernel path)
   int host_slabs;        // member slabs of the host-buffer entry point (copy/compute overlap); 1 = no pipelining, 0 = auto
@@ -961,14 +965,14 @@ static void launch_state_sweep(awfl_handle *h, const Geom &g, int dir, int mode,
   AWFL_ORD_DISPATCH(march_state(h->stream, g, h->ph, a, dir, mode, dir == 2 ? vtable_home(h, mode, false) : 0));
 }
 
-static void launch_tracer_sweep(awfl_handle *h, const Geom &g, int dir, TracerSweepArgs a) {
-  if (g.nt == 0) return;
+static void launch_tracer_sweep(awfl_handle *h, const Geom &g, int dir, TracerSweepArgs a, int first_tracer = 0) {
+  if (g.nt <= first_tracer) return;
   // the grid carries (tracer, line index, segment) in blockIdx.z, which CUDA limits to 65535: tall grids with many tracers
   // (nz = 128, nx >= 768: 2048 work items per tracer) go in chunks of tracers
   static const int zmax = getenv("AWFL_GRID_Z_MAX") && atoi(getenv("AWFL_GRID_Z_MAX")) > 0 ? atoi(getenv("AWFL_GRID_Z_MAX")) : 65535;   // tests
   int per_launch = zmax >> (a.labits + a.sbits);
   if (per_launch < 1) per_launch = 1;
-  for (int t0 = 0; t0 < g.nt; t0 += per_launch) {
+  for (int t0 = first_tracer; t0 < g.nt; t0 += per_launch) {
     a.tr0 = t0; a.ntr = g.nt - t0 < per_launch ? g.nt - t0 : per_launch;
     ProfScope ps(h, KC_TRACER_X + dir);
     AWFL_ORD_DISPATCH(march_tracer(h->stream, g, a, dir, dir == 2 ? vtable_home(h, 1, true) : 0));
@@ -1009,6 +1013,9 @@ static void run_stage(awfl_handle *h, const Geom &g, const double *qin, const do
     s.dz = h->dz; s.grav_var = h->grav_var; s.vtab = h->vtab; s.rdz = h->rdz; s.pcache = h->pcache; s.vst = h->shared_grid ? 1 : g.nens;
     s.a = a; s.b = b; s.c = b * dt_full; s.first = d == 0; s.sbits = sbits_state(h, g, dir, nn[dir]); s.labits = labits_for(h, dir);
     s.seg_only = -1; s.general_2d = h->general_2d;
+    // 2-D: the first tracer rides in the state march, in the slot the reconstruction of v leaves free (awfl_march.cuh RingF)
+    const int fused = g.sim2d && !h->general_2d && g.nt > 0 && (h->fused_tracer >> (dir == 2 ? 1 : 0) & 1) ? 1 : 0;
+    s.fused_tracer = fused; s.tflux = h->tflux[dir];
     TracerSweepArgs t;
     t.qin = qin; t.mflux = h->mflux[dir]; t.tflux = h->tflux[dir]; t.vtab = h->vtab; t.vst = s.vst; t.sbits = sbits_fill(sbits_for(h, nn[dir]), nn[dir], (march_lines(g, dir) + 1) / 2 * g.nt); t.labits = s.labits;
     t.seg_only = -1;
@@ -1020,12 +1027,12 @@ static void run_stage(awfl_handle *h, const Geom &g, const double *qin, const do
         if (upload_cvpage(h, p) != 0) { h->err = "upload of a vertical-table page failed"; return; }
         s.seg_only = t.seg_only = p;
         launch_state_sweep(h, g, dir, last ? mode : 0, s);
-        launch_tracer_sweep(h, g, dir, t);
+        launch_tracer_sweep(h, g, dir, t, fused);
       }
       continue;
     }
     launch_state_sweep(h, g, dir, last ? mode : 0, s);
-    launch_tracer_sweep(h, g, dir, t);
+    launch_tracer_sweep(h, g, dir, t, fused);
   }
   if (g.nt > 0 && g.sim2d && mode == 1 && !fct_start && h->fused_fct) {
     // fused FCT + update (2-D): strips of W columns, enough level segments for a few waves of one-warp blocks
@@ -1074,6 +1081,8 @@ const char *awfl_dycore_name(void) { return "SSPRK3+WENO+FV A-grid"; }
 const char *awfl_last_error(const awfl_handle *h) { return h ? h->err.c_str() : g_create_err.c_str(); }
 
 long awfl_launch_count(const awfl_handle *h) { return h->launches; }
+
+int awfl_fused_tracer(const awfl_handle *h) { return h->g.sim2d && !h->general_2d && h->g.nt > 0 ? h->fused_tracer : 0; }
 
 int awfl_table_home(const awfl_handle *h) { return h->use_cvtab ? 1 : (h->use_cvpage ? 4 : (h->shared_grid ? 3 : 2)); }
 
@@ -1209,6 +1218,10 @@ int awfl_create(const awfl_config *cfg, awfl_handle **out) {
   h->stage_fields = nullptr; h->stage_out = nullptr; h->tmp_state = nullptr; h->halo_pressure = nullptr;
   { const char *ev = getenv("AWFL_FUSED_FCT"); h->fused_fct = !(ev && atoi(ev) == 0); }
   { const char *ev = getenv("AWFL_GENERAL_2D"); h->general_2d = ev && atoi(ev) == 1; }
+  // measured (profiles/r02G_fused_tracer_ab.txt): both marches up to ord 7; at ord 9 the vertical march, already at the
+  // register cap with its dense per-level tables, loses more than the tracer march costs
+  h->fused_tracer = cfg->ord <= AWFL_FUSED_TRACER_Z_MAX_ORD ? 3 : 1;
+  { const char *ev = getenv("AWFL_FUSED_TRACER"); if (ev) h->fused_tracer = atoi(ev) & 3; }
   h->s_in = nullptr; h->s_out = nullptr; h->host_last_ncycles = 0; h->host_mispredictions = 0;
   {
     // member slabs of awfl_time_step_host: chosen from the grid by default (host_slab_count); AWFL_HOST_SLABS overrides

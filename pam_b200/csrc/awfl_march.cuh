@@ -21,11 +21,16 @@ namespace awfl {
 // Ring fields in marching order: the acoustic pair first, then the advected quantities, then density. The RECONSTRUCTED
 // fields are contiguous from 0. In a 2-D run (S2D) v is not one of them: the reference zeroes the v tendency there
 // (Dycore.h:565), so the flux of v -- one of the six reconstructions per cell and direction -- never reaches a result.
-// v then sits behind theta, only for the stage combination of its round-tripped value.
-enum { RF_COUNT = 7 };
-template <bool S2D> struct RingF {
-  static constexpr int M = 0, P = 1, U = 2, V = S2D ? 5 : 3, W = S2D ? 3 : 4, T = S2D ? 4 : 5, R = 6;
-  static constexpr int NVAR = S2D ? 5 : 6;                   // reconstructed: M, P, U, [V,] W, T
+// v then sits behind the reconstructed fields, only for the stage combination of its round-tripped value. The slot v
+// leaves free in the pairs / triples of reconstructions can carry the mixing ratio of the FIRST TRACER (TRQ): its
+// interface flux (the tracer part of Dycore.h:381-385 / :513-517) then comes out of the state march and the tracer march
+// runs for the other tracers only.
+enum { RF_COUNT = 8 };
+template <bool S2D, bool TRQ> struct RingF {
+  static_assert(S2D || !TRQ, "the state march carries a tracer only in its 2-D form");
+  static constexpr int M = 0, P = 1, U = 2, W = S2D ? 3 : 4, T = S2D ? 4 : 5, Q = 5, V = S2D ? (TRQ ? 6 : 5) : 3, R = 7;
+  static constexpr int NVS = S2D ? 5 : 6;                    // reconstructed state quantities: M, P, U, [V,] W, T
+  static constexpr int NVAR = NVS + (TRQ ? 1 : 0);           // ... + the first tracer's mixing ratio
 };
 
 #ifndef AWFL_MINB5
@@ -75,7 +80,7 @@ template <int ORD> struct MarchCfg {
 // r02j_pow_variants.txt. The library pair's dependency chains are shorter; the UMOVs ride the uniform datapath.)
 __device__ __forceinline__ double pow_pos(double x, double g) { return exp(g * log(x)); }
 
-struct Raw { double r, ru, rv, rw, rt, p; };
+struct Raw { double r, ru, rv, rw, rt, p, tq; };
 
 // 8-byte asynchronous global -> shared copy (LDGSTS). Unlike a load into a register it is not tracked by the register
 // scoreboard, so it stays in flight across the call to weno_ring (a CALL waits for every pending register load:
@@ -186,12 +191,20 @@ template <int ORD> struct MatSel<ORD, 3> {
 #ifndef AWFL_MAXNREG_H
 #define AWFL_MAXNREG_H 168
 #endif
-#define AWFL_STATE_BOUNDS __launch_bounds__(MT) __maxnreg__(ORD == 3 ? 128 : (ORD == 5 ? (DIR == 2 ? AWFL_MAXNREG_Z : AWFL_MAXNREG_H) : 255))
-template <int ORD, int DIR, int MODE, int VT, bool S2D>
+// The 2-D vertical march that carries the first tracer (TRQ) keeps the overflow-proof reconstruction behind a call inside
+// its rolled loop: at 144 registers it spills 184 B and runs 9.2 ms on C2, at 168 none and 6.97 ms (r02G).
+#ifndef AWFL_MAXNREG_ZQ
+#define AWFL_MAXNREG_ZQ 168
+#endif
+#ifndef AWFL_MAXNREG_ZQ3
+#define AWFL_MAXNREG_ZQ3 128
+#endif
+#define AWFL_STATE_BOUNDS __launch_bounds__(MT) __maxnreg__(ORD == 3 ? (DIR == 2 && TRQ ? AWFL_MAXNREG_ZQ3 : 128) : (ORD == 5 ? (DIR == 2 ? (TRQ ? AWFL_MAXNREG_ZQ : AWFL_MAXNREG_Z) : AWFL_MAXNREG_H) : 255))
+template <int ORD, int DIR, int MODE, int VT, bool S2D, bool TRQ>
 __global__ void AWFL_STATE_BOUNDS
 k_march_state(const Geom g, const Phys ph, const SweepArgs a) {
-  using F = RingF<S2D>;
-  constexpr int NVAR = F::NVAR;
+  using F = RingF<S2D, TRQ>;
+  constexpr int NVAR = F::NVAR, NVS = F::NVS;
   // 2-D: v is only needed where the stage is combined (its round-tripped value), not by a sweep that accumulates tendencies
   constexpr bool NEED_V = !(S2D && MODE == 0);
   constexpr int HS = (ORD + 1) / 2;
@@ -235,6 +248,7 @@ k_march_state(const Geom g, const Phys ph, const SweepArgs a) {
     x.r = __ldg(qp); x.ru = __ldg(qp + nc); x.rw = __ldg(qp + 3 * nc);
     x.rv = NEED_V ? __ldg(qp + 2 * nc) : 0.0;
     x.rt = __ldg(qp + 4 * nc);
+    x.tq = TRQ ? __ldg(qp + 5 * nc) : 0.0;                              // the first tracer: field NS of the stage input
     // the pressure C0 (rho theta)^gamma of a cell is the same in every direction of a stage: the x march (always the
     // first sweep) computes it, the other marches read it back -- one x^gamma (~160 instructions) per cell and stage
     // instead of one per direction
@@ -278,6 +292,8 @@ k_march_state(const Geom g, const Phys ph, const SweepArgs a) {
     if (NEED_V) rb[(F::V * ORD) * MT + so] = x.rv * rinv;
     rb[(F::W * ORD) * MT + so] = w;
     rb[(F::T * ORD) * MT + so] = x.rt * rinv;
+    // mixing ratio, Dycore.h:320; a wall ghost repeats the boundary cell's (zero gradient, Dycore.h:674-677: rinv is still that cell's)
+    if (TRQ) rb[(F::Q * ORD) * MT + so] = x.tq * rinv;
     rb[(F::R * ORD) * MT + so] = r;
   };
 
@@ -334,7 +350,7 @@ k_march_state(const Geom g, const Phys ph, const SweepArgs a) {
 #pragma unroll
       for (int i = 0; i < NV; i++) {
         const int v = g0 + i;
-        if (v > 0 && (NTAIL == 0 || v < NVAR)) {
+        if (v > 0 && v < NVS) {
           if (ld_t) cp_async8(pf_s, pf_t);
           if (ld_q) cp_async8(pf_s + MT, pf_q);   // qout may alias qbase: read before the write below
           pf_s += 2 * MT;
@@ -355,6 +371,16 @@ k_march_state(const Geom g, const Phys ph, const SweepArgs a) {
     // one reconstructed variable: v = 0 rho*u_n, 1 p (the acoustic pair closes interface c), then the advected u, [v,] w, theta
     auto handle = [&](int v, double E, double O) {
       if (v == 0) { mRs = E - O; mLns = E + O; return; }
+      if (TRQ && v == NVS) {
+        // the first tracer: flux = mass flux x upwind edge value of the mixing ratio, zero through the walls
+        // (Dycore.h:381-385 / :513-517, :477, :496); no operands, no update here -- the FCT kernels finish the tracers
+        double *const feq = fpv + (NS + 3) * MT;               // the right-edge slot v leaves free
+        double Fq = rn * (up ? feq[0] : E - O);
+        feq[0] = E + O;
+        if (wall) Fq = 0.0;
+        if (flux_on && (c < it.c1 || (DIR == 2 && c == n))) a.tflux[it.base + (long)c * sd] = Fq;
+        return;
+      }
       // this variable's cursors; the shared ones move on to the next variable
       double *const po_l = po, *const fl_l = fl, *const fe_l = fe;
       const double *const sg_l = sg, *const rl_l = rl;
@@ -416,6 +442,14 @@ k_march_state(const Geom g, const Phys ph, const SweepArgs a) {
       if (ld_t || ld_q) {
         if (PRE_ALL) cp_async_wait_left((NVAR - 1 - v0) / NV);   // the later groups may still be in flight
         else cp_async_wait_left(1);                              // all but the group just started
+      }
+      if (TRQ && v0 + NV == NVAR) {
+        // tracers carry arbitrary units (number concentrations ...): a magnitude that overflows the fast weights gives NaN
+        // or inf and goes through the overflow-proof ones, as in the tracer march
+        if (!(fabs(eo.E[NV - 1]) <= 1.7976931348623157e308)) {
+          const EOn<1> sf = weno_ring_safe<ORD>(rb + (F::Q * ORD) * MT, head, mat);
+          eo.E[NV - 1] = sf.E[0]; eo.O[NV - 1] = sf.O[0];
+        }
       }
 #pragma unroll
       for (int i = 0; i < NV; i++) handle(v0 + i, eo.E[i], eo.O[i]);

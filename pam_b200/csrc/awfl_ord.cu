@@ -40,14 +40,15 @@ void OrdLaunch<ORD>::march_state(cudaStream_t s, const Geom &g, const Phys &ph, 
   // x and y sweeps only ever accumulate (MODE 0); the z sweep is always the last of a stage (MODE 1 or 2). A 2-D run
   // (ny == 1, no y sweep) takes the kernels that leave the reconstruction of v out (RingF in awfl_march.cuh) unless the
   // handle asks for the general ones
-  const bool s2d = g.sim2d && !a.general_2d;
-#define AWFL_STATE_CASE(D, M, V)                                                       \
-  do {                                                                                 \
-    if (s2d) AWFL_LAUNCH_MARCH((k_march_state<ORD, D, M, V, true>), B, g, ph, a);      \
-    else AWFL_LAUNCH_MARCH((k_march_state<ORD, D, M, V, false>), B, g, ph, a);         \
+  const bool s2d = g.sim2d && !a.general_2d, trq = s2d && a.fused_tracer;
+#define AWFL_STATE_CASE(D, M, V)                                                              \
+  do {                                                                                        \
+    if (trq) AWFL_LAUNCH_MARCH((k_march_state<ORD, D, M, V, true, true>), B, g, ph, a);       \
+    else if (s2d) AWFL_LAUNCH_MARCH((k_march_state<ORD, D, M, V, true, false>), B, g, ph, a); \
+    else AWFL_LAUNCH_MARCH((k_march_state<ORD, D, M, V, false, false>), B, g, ph, a);         \
   } while (0)
   if (dir == 0) AWFL_STATE_CASE(0, 0, 0);
-  else if (dir == 1) AWFL_LAUNCH_MARCH((k_march_state<ORD, 1, 0, 0, false>), B, g, ph, a);
+  else if (dir == 1) AWFL_LAUNCH_MARCH((k_march_state<ORD, 1, 0, 0, false, false>), B, g, ph, a);
   else if (mode == 1) {
     if (vt == 1) AWFL_STATE_CASE(2, 1, 1);
     else if (vt == 3) AWFL_STATE_CASE(2, 1, 3);
@@ -73,19 +74,18 @@ void OrdLaunch<ORD>::march_tracer(cudaStream_t s, const Geom &g, const TracerSwe
 template <int ORD>
 void OrdLaunch<ORD>::configure() {
   constexpr size_t BS = MarchCfg<ORD>::SMEM_STATE, BT = MarchCfg<ORD>::SMEM_TRACER;
-  configure_march(k_march_state<ORD, 0, 0, 0, false>, BS);
-  configure_march(k_march_state<ORD, 0, 0, 0, true>, BS);
-  configure_march(k_march_state<ORD, 1, 0, 0, false>, BS);
-  configure_march(k_march_state<ORD, 2, 1, 1, false>, BS);
-  configure_march(k_march_state<ORD, 2, 1, 2, false>, BS);
-  configure_march(k_march_state<ORD, 2, 1, 3, false>, BS);
-  configure_march(k_march_state<ORD, 2, 2, 1, false>, BS);
-  configure_march(k_march_state<ORD, 2, 2, 2, false>, BS);
-  configure_march(k_march_state<ORD, 2, 1, 1, true>, BS);
-  configure_march(k_march_state<ORD, 2, 1, 2, true>, BS);
-  configure_march(k_march_state<ORD, 2, 1, 3, true>, BS);
-  configure_march(k_march_state<ORD, 2, 2, 1, true>, BS);
-  configure_march(k_march_state<ORD, 2, 2, 2, true>, BS);
+#define AWFL_CONFIGURE_2D(D, M, V)                                   \
+  configure_march(k_march_state<ORD, D, M, V, false, false>, BS);    \
+  configure_march(k_march_state<ORD, D, M, V, true, false>, BS);     \
+  configure_march(k_march_state<ORD, D, M, V, true, true>, BS)
+  AWFL_CONFIGURE_2D(0, 0, 0);
+  configure_march(k_march_state<ORD, 1, 0, 0, false, false>, BS);
+  AWFL_CONFIGURE_2D(2, 1, 1);
+  AWFL_CONFIGURE_2D(2, 1, 2);
+  AWFL_CONFIGURE_2D(2, 1, 3);
+  AWFL_CONFIGURE_2D(2, 2, 1);
+  AWFL_CONFIGURE_2D(2, 2, 2);
+#undef AWFL_CONFIGURE_2D
   configure_march(k_march_tracer<ORD, 0, 0>, BT);
   configure_march(k_march_tracer<ORD, 1, 0>, BT);
   configure_march(k_march_tracer<ORD, 2, 1>, BT);

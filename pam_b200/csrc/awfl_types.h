@@ -38,6 +38,8 @@ struct SweepArgs {
   int first;              // 1: this is the first sweep of the stage (tend is written, not accumulated)
   int sbits, labits;      // grid encoding (decode_item): 2^sbits segments per line, labits bits for the first line index
   int seg_only;           // >= 0: only this segment of every line works, the other blocks leave at once (paged vertical tables)
+  double *tflux;          // fused_tracer: interface fluxes of the first tracer in this direction
+  int fused_tracer;       // 2-D: the state march carries the first tracer (its flux goes to tflux; the tracer march skips it)
   int general_2d;         // 2-D run on the general kernels, which reconstruct v too (AWFL_GENERAL_2D=1 at create time: A/B and agreement tests)
 };
 

@@ -257,6 +257,10 @@ class Dycore:
         """1: vertical matrices in the constant bank, 3: unit-stride global table, 2: member-strided global table."""
         return int(self.lib.awfl_table_home(self.h))
 
+    def fused_tracer(self):
+        """Bit 0 / bit 1: the x / z state march carries the first tracer (2-D runs); 0 otherwise."""
+        return int(self.lib.awfl_fused_tracer(self.h))
+
     def host_mispredictions(self):
         """Calls of time_step_host whose predicted sub-cycle count was wrong (redone un-overlapped)."""
         return self.lib.awfl_host_mispredictions(self.h)

@@ -57,12 +57,17 @@ def flops_per_cell_update(ord, nt, ndir):
     return 3 * flops_per_cell_stage(ord, nt, ndir)
 
 
-def state_sweep_flops_per_cell(ord, sim2d=False):
+def state_sweep_flops_per_cell(ord, sim2d=False, fused_tracer=False):
     """Reference flops of the part of the flux kernel the state sweep replaces, per cell and direction: 4 acoustic + 4
     advective reconstructions (3 in a 2-D run, see flops_per_cell_stage), stencil products, characteristics, the fluxes,
-    divergence."""
+    divergence -- plus, where the march carries the first tracer, that tracer's share of the tracer march."""
     adv = 3 if sim2d else 4
-    return (4 + adv) * recon_flops(ord)[0] + 2 * ord + 12 + 2 * adv + 3 * (1 + adv)
+    return (4 + adv) * recon_flops(ord)[0] + 2 * ord + 12 + 2 * adv + 3 * (1 + adv) + (tracer_sweep_flops_per_cell(ord) if fused_tracer else 0)
+
+
+def tracer_sweep_flops_per_cell(ord):
+    """Reference flops of one tracer's flux per cell and direction: one reconstruction, mixing ratio, upwind flux."""
+    return recon_flops(ord)[0] + 4
 
 
 def bytes_per_cell_update(nt):
@@ -70,7 +75,8 @@ def bytes_per_cell_update(nt):
     return 64 * (5 + nt)
 
 
-def state_sweep_bytes_per_cell(last):
+def state_sweep_bytes_per_cell(last, fused_tracer=False):
     """Compulsory bytes of one state sweep launch per cell: read 5 conserved fields; a non-final sweep writes 5 partial
-    tendencies + 1 mass flux; the final sweep reads 5 partial tendencies + 5 base fields, writes 5 fields + 1 mass flux."""
-    return 8 * (5 + 5 + 1) if not last else 8 * (5 + 5 + 5 + 5 + 1)
+    tendencies + 1 mass flux; the final sweep reads 5 partial tendencies + 5 base fields, writes 5 fields + 1 mass flux. A
+    march that carries the first tracer also reads that tracer and writes its flux."""
+    return (8 * (5 + 5 + 1) if not last else 8 * (5 + 5 + 5 + 5 + 1)) + (16 if fused_tracer else 0)

@@ -357,6 +357,37 @@ def test_segment_length_does_not_change_a_bit(ord, ny, monkeypatch):
             assert np.array_equal(out["100000"][k], out[seg][k]), (seg, k)
 
 
+@pytest.mark.parametrize("ord", [3, 5, 7, 9])
+@pytest.mark.parametrize("nt,grid,per_ens", [(1, "tanh", False), (10, "tanh", False), (1, "equal", False), (1, "tanh", True)])
+def test_first_tracer_in_the_2d_state_march_agrees_with_the_tracer_march(ord, nt, grid, per_ens, monkeypatch):
+    """2-D: the first tracer's interface flux comes out of the state marches (in the slot the reconstruction of v leaves
+    free), the tracer march runs for the others. AWFL_FUSED_TRACER=0 sends every tracer through the tracer march: same
+    formulas on the same inputs through other instances of the reconstruction -> equal to round-off."""
+    case = _case(nz=14, nx=18, nens=40, nt=nt, grid=grid, per_ens=per_ens)
+    out = {}
+    for fused in ("3", "0"):                     # 3 = both marches carry it, whatever the default of the order is
+        monkeypatch.setenv("AWFL_FUSED_TRACER", fused)
+        c, d = H.make_gpu(case, ord, crm_dt=2.0)
+        d.declare_current_profile_as_hydrostatic(c)
+        for _ in range(2):
+            d.timeStep(c)
+        out[fused] = H.gpu_fields(c)
+    out["1"] = out["3"]
+    un = float(np.linalg.norm(out["0"]["uvel"]))
+    for k in out["0"]:
+        a, b = out["1"][k], out["0"][k]
+        floor = 1e-3 * un if k in ("uvel", "vvel", "wvel") else 1e-300
+        assert np.linalg.norm(a - b) <= 1e-13 * max(np.linalg.norm(b), floor), k
+    o = H.make_oracle(case, ord, crm_dt=2.0)
+    o.declare_hydrostatic()
+    for _ in range(2):
+        o.time_step()
+    ref = o.get_fields()
+    fl = field_floors(ref)
+    for k in ref:
+        assert rel_l2(out["1"][k], ref[k], fl[k]) <= 2 * TOL_STEP, (k, rel_l2(out["1"][k], ref[k], fl[k]))
+
+
 def test_errors_are_reported_not_swallowed():
     from pam_b200 import PamCoupler, Dycore
     c = PamCoupler("cuda:0")

@@ -107,6 +107,9 @@ def test_roofline_counts_are_frozen():
     assert roofline.state_sweep_flops_per_cell(5) == 8 * 295 + 10 + 12 + 8 + 15
     # 2-D: the reconstruction and flux of v, which the reference computes and discards (Dycore.h:565), is not algorithmic work
     assert roofline.state_sweep_flops_per_cell(5, sim2d=True) == 7 * 295 + 10 + 12 + 6 + 12
+    # ... and a 2-D march that carries the first tracer counts that tracer's share of the tracer march
+    assert roofline.state_sweep_flops_per_cell(5, sim2d=True, fused_tracer=True) == 7 * 295 + 10 + 12 + 6 + 12 + 295 + 4
+    assert roofline.state_sweep_bytes_per_cell(last=True, fused_tracer=True) == 8 * 21 + 16
     assert roofline.flops_per_cell_stage(5, 1, 3) == 3 * (9 * 295 + 10 + 12 + 10 + 18) + 5 + 4 + 1 + 30 + 30
     assert roofline.flops_per_cell_stage(5, 1, 2) == 2 * (8 * 295 + 10 + 12 + 8 + 15) + 5 + 4 + 1 + 30 + 30
 

@@ -577,14 +577,17 @@ def test_scratch_memory_is_never_read_before_it_is_written_and_steps_repeat_bit_
         assert np.array_equal(a, runs[0][2][k]), k       # host path == resident path
 
 
-@pytest.mark.parametrize("nt", [1, 10])
-def test_paged_vertical_table_gives_the_bits_of_the_global_table(nt, monkeypatch):
+@pytest.mark.parametrize("nt,fused", [(1, None), (10, None), (1, "3"), (10, "3")])
+def test_paged_vertical_table_gives_the_bits_of_the_global_table(nt, fused, monkeypatch):
     """ord 9 at 40 levels: the per-level table (42 x 206 doubles) does not fit the constant bank as a whole, so the z marches
     run segment by segment behind the upload of the levels each segment reads (table home 4). Same numbers, same
     arithmetic as the global-memory table (home 3): identical bits, through the resident step, the tendency entry point
-    and the host-buffer entry point (whose slabs, on several streams, read the global copy)."""
+    and the host-buffer entry point (whose slabs, on several streams, read the global copy). fused = "3": the vertical
+    state march carries the first tracer (not the default at ord 9), page by page like the rest."""
     import torch
     case = _case(nz=40, nx=10, nens=40, nt=nt)
+    if fused:
+        monkeypatch.setenv("AWFL_FUSED_TRACER", fused)
     out = {}
     for no_page in ("0", "1"):
         if no_page == "1":

@@ -26,6 +26,10 @@ int main(int argc, char **argv) {
   const size_t bytes = sizeof(double) * nf * rows * nens;
   double *h_in, *h_out, *d_in, *d_out;
   CK(cudaHostAlloc((void **)&h_in, bytes, cudaHostAllocMapped));
+  // argv[2] = 1: in place, like awfl_time_step_host (results overwrite the inputs: the two directions touch the SAME host
+  // rows, other columns, at the same time -- a slab's results go out while a later slab's inputs come in)
+  const bool inplace = argc > 2 && atoi(argv[2]) == 1;
+  if (inplace) h_out = h_in; else
   CK(cudaHostAlloc((void **)&h_out, bytes, cudaHostAllocMapped));
   CK(cudaMalloc((void **)&d_in, bytes));
   CK(cudaMalloc((void **)&d_out, bytes));
@@ -52,7 +56,15 @@ int main(int argc, char **argv) {
               CK(cudaMemcpy2DAsync(d_in + v * rows * nens + e0, pitch, h_in + v * rows * nens + e0, pitch, sizeof(double) * ne, rows, cudaMemcpyHostToDevice, s_in));
             else k_slab_copy<<<grid, 256, 0, s_in>>>((double2 *)d_in, (const double2 *)h_in, nf, rows, nens / 2, e0 / 2, ne / 2);
           }
-          if (dirs & 2) {
+          if ((dirs & 2) && inplace && grid == 0 && dirs == 3) {
+            // the results of slab s-3 (the pipeline's depth) leave while slab s arrives
+            const int so = s - 3;
+            if (so >= 0) {
+              const int u0 = (int)((long)tiles * so / P), u1 = (int)((long)tiles * (so + 1) / P);
+              for (int v = 0; v < nf; v++)
+                CK(cudaMemcpy2DAsync(h_out + v * rows * nens + 32 * u0, pitch, d_out + v * rows * nens + 32 * u0, pitch, sizeof(double) * 32 * (u1 - u0), rows, cudaMemcpyDeviceToHost, s_out));
+            }
+          } else if (dirs & 2) {
             if (grid == 0) for (int v = 0; v < nf; v++)
               CK(cudaMemcpy2DAsync(h_out + v * rows * nens + e0, pitch, d_out + v * rows * nens + e0, pitch, sizeof(double) * ne, rows, cudaMemcpyDeviceToHost, s_out));
             else k_slab_copy<<<grid, 256, 0, s_out>>>((double2 *)h_out, (const double2 *)d_out, nf, rows, nens / 2, e0 / 2, ne / 2);
@@ -102,7 +114,7 @@ int main(int argc, char **argv) {
   // check that the kernel-written host buffer holds the device pattern
   const unsigned char *hb = (const unsigned char *)h_out;
   size_t bad = 0;
-  for (size_t i = 0; i < bytes; i += 4097) bad += hb[i] != 1;
+  if (!inplace) for (size_t i = 0; i < bytes; i += 4097) bad += hb[i] != 1;
   printf("host buffer check: %zu mismatches\n", bad);
   return bad != 0;
 }

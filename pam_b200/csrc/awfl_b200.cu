@@ -668,6 +668,7 @@ struct awfl_handle {
   double *stage_fields;  // staging buffer for the host-buffer entry point (5+nt fields)
   int host_last_ncycles;      // sub-cycle count derived by the previous awfl_time_step_host (0 = none yet): the prediction
   long host_mispredictions;   // calls whose prediction was wrong and were redone un-overlapped
+  bool tracer_pairs;     // tracer march: two tracers per warp on one line instead of two lines of one tracer (AWFL_TRACER_PAIRS)
   int fused_tracer;      // 2-D: the first tracer is reconstructed by the state march of x (bit 0) / z (bit 1) instead of the tracer march (AWFL_FUSED_TRACER)
   bool general_2d;       // 2-D on the general state marches (AWFL_GENERAL_2D=1; see SweepArgs::general_2d)
   bool fused_fct;        // 2-D: fused FCT + tracer update kernel (AWFL_FUSED_FCT=0 selects the two-kernel path)
@@ -972,10 +973,24 @@ static void launch_tracer_sweep(awfl_handle *h, const Geom &g, int dir, TracerSw
   static const int zmax = getenv("AWFL_GRID_Z_MAX") && atoi(getenv("AWFL_GRID_Z_MAX")) > 0 ? atoi(getenv("AWFL_GRID_Z_MAX")) : 65535;   // tests
   int per_launch = zmax >> (a.labits + a.sbits);
   if (per_launch < 1) per_launch = 1;
-  for (int t0 = first_tracer; t0 < g.nt; t0 += per_launch) {
+  const int vt = dir == 2 ? vtable_home(h, 1, true) : 0;
+  // Two tracers per warp on one line share the line's density, its reciprocal and the mass flux (h->tracer_pairs); an odd
+  // tracer is left for a launch of the two-lines-per-warp form.
+  int t0 = first_tracer;
+  if (h->tracer_pairs) {
+    const int npair_total = (g.nt - first_tracer) / 2;
+    for (int p0 = 0; p0 < npair_total; p0 += per_launch) {
+      const int np = npair_total - p0 < per_launch ? npair_total - p0 : per_launch;
+      a.tr0 = first_tracer + 2 * p0; a.ntr = 2 * np;
+      ProfScope ps(h, KC_TRACER_X + dir);
+      AWFL_ORD_DISPATCH(march_tracer(h->stream, g, a, dir, vt, true));
+    }
+    t0 = first_tracer + 2 * npair_total;
+  }
+  for (; t0 < g.nt; t0 += per_launch) {
     a.tr0 = t0; a.ntr = g.nt - t0 < per_launch ? g.nt - t0 : per_launch;
     ProfScope ps(h, KC_TRACER_X + dir);
-    AWFL_ORD_DISPATCH(march_tracer(h->stream, g, a, dir, dir == 2 ? vtable_home(h, 1, true) : 0));
+    AWFL_ORD_DISPATCH(march_tracer(h->stream, g, a, dir, vt, false));
   }
 }
 
@@ -1222,6 +1237,7 @@ int awfl_create(const awfl_config *cfg, awfl_handle **out) {
   // register cap with its dense per-level tables, loses more than the tracer march costs
   h->fused_tracer = cfg->ord <= AWFL_FUSED_TRACER_Z_MAX_ORD ? 3 : 1;
   { const char *ev = getenv("AWFL_FUSED_TRACER"); if (ev) h->fused_tracer = atoi(ev) & 3; }
+  { const char *ev = getenv("AWFL_TRACER_PAIRS"); h->tracer_pairs = !(ev && atoi(ev) == 0); }
   h->s_in = nullptr; h->s_out = nullptr; h->host_last_ncycles = 0; h->host_mispredictions = 0;
   {
     // member slabs of awfl_time_step_host: chosen from the grid by default (host_slab_count); AWFL_HOST_SLABS overrides

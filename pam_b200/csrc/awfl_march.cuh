@@ -476,28 +476,38 @@ k_march_state(const Geom g, const Phys ph, const SweepArgs a) {
 // Tracer march: the tracer part of Dycore.h:381-385 / :434-438 / :513-517. flux = massflux * upwind WENO edge value of
 // (tracer/rho), cell-centred like the state march. Work item = (tracer, line, segment, ensemble tile).
 // ---------------------------------------------------------------------------------------------------------------
-template <int ORD, int DIR, int VT>
+// PAIR = false: a warp marches two adjacent lines of ONE tracer; PAIR = true: one line of TWO tracers (tr, tr+1), which
+// share the line's density, its reciprocal and the mass flux -- loaded and computed once per cell instead of per tracer.
+template <int ORD, int DIR, int VT, bool PAIR>
 __global__ void __launch_bounds__(MT, MarchCfg<ORD>::MINB_TR)
 k_march_tracer(const Geom g, const TracerSweepArgs a) {
   constexpr int HS = (ORD + 1) / 2;
-  constexpr int NL = 2;                                       // lines marched together by one warp
+  constexpr int NL = 2;                                       // reconstructions marched together by one warp
   extern __shared__ double ring_smem[];
   Item it;                                                    // one warp per block (see k_march_state)
   // the two lines of a warp are adjacent levels k, k+1 for the horizontal marches and adjacent columns i, i+1 for the
   // vertical march (an odd count repeats the last line: the same values are written twice)
-  if (!decode_item<DIR, DIR == 2 ? 1 : NL, DIR == 2 ? NL : 1>(g, a.sbits, a.labits, it, DIR == 2 ? a.seg_only : -1)) return;
-  const int tr = a.tr0 + it.tr;
-  if (it.tr >= a.ntr || tr >= g.nt) return;
+  if (!decode_item<DIR, (PAIR || DIR == 2) ? 1 : NL, (!PAIR && DIR == 2) ? NL : 1>(g, a.sbits, a.labits, it, DIR == 2 ? a.seg_only : -1)) return;
+  const int tr = a.tr0 + (PAIR ? 2 * it.tr : it.tr);
+  if ((PAIR ? 2 * it.tr + 1 : it.tr) >= a.ntr || tr + (PAIR ? 1 : 0) >= g.nt) return;   // pair launches carry an even count
   const int n = DIR == 0 ? g.nx : (DIR == 1 ? g.ny : g.nz);
   const long sd = stride_of(DIR, g);
   const size_t nc = (unsigned)g.ncell;                        // < 2^32, see k_march_state
   const double *__restrict__ rho = a.qin;
-  const double *__restrict__ tq = a.qin + (long)(NS + tr) * nc;
-  double *__restrict__ fl = a.tflux + (long)tr * (DIR == 2 ? nc + nc / g.nz : nc);
-  long base[NL];
+  const size_t fstride = DIR == 2 ? nc + nc / g.nz : nc;      // one tracer's interface fluxes of this direction
+  const double *__restrict__ tq = a.qin + (size_t)(NS + tr) * nc;   // first (or only) tracer of the warp
+  double *__restrict__ fl = a.tflux + (size_t)tr * fstride;
+  // offsets of reconstruction v: the line (base) and, in a pair, the tracer (tb into the tracer fields, fb into the fluxes)
+  long base[NL], tb[NL], fb[NL];
   base[0] = it.base;
-  if (DIR == 2) base[1] = it.lb + 1 < g.nx ? it.base + g.nens : it.base;
+  if (PAIR) base[1] = it.base;
+  else if (DIR == 2) base[1] = it.lb + 1 < g.nx ? it.base + g.nens : it.base;
   else base[1] = it.la + 1 < g.nz ? it.base + (long)g.ny * g.nx * g.nens : it.base;
+#pragma unroll
+  for (int v = 0; v < NL; v++) {
+    tb[v] = PAIR ? base[v] + (long)(v * nc) : base[v];
+    fb[v] = PAIR ? base[v] + (long)(v * fstride) : base[v];
+  }
   double *const rb = ring_smem + threadIdx.x;                 // ring of line v at rb[(v*ORD + slot)*MT]
   double *const stg = rb + (NL * ORD) * MT;                   // staged next cell (tracer, rho) and next mass flux, per line
   const long voff = a.vst > 1 ? it.e : 0;
@@ -513,28 +523,43 @@ k_march_tracer(const Geom g, const TracerSweepArgs a) {
 #pragma unroll
     for (int s = 0; s < ORD; s++) {
       const long o = cell_off(cs0 + s);
+      if (PAIR) {
+        const double rinv = rcp_pos(__ldg(rho + base[0] + o));   // Dycore.h:320
 #pragma unroll
-      for (int v = 0; v < NL; v++) rb[(v * ORD + s) * MT] = __ldg(tq + base[v] + o) * rcp_pos(__ldg(rho + base[v] + o));   // Dycore.h:320
+        for (int v = 0; v < NL; v++) rb[(v * ORD + s) * MT] = __ldg(tq + tb[v] + o) * rinv;
+      } else {
+#pragma unroll
+        for (int v = 0; v < NL; v++) rb[(v * ORD + s) * MT] = __ldg(tq + tb[v] + o) * rcp_pos(__ldg(rho + base[v] + o));   // Dycore.h:320
+      }
     }
   }
+  // staging of the next cell: PAIR: [tracer 0, tracer 1, rho, mass flux]; else per line [tracer, rho, mass flux]
   double Rp[NL] = {0.0, 0.0}, rn[NL] = {0.0, 0.0};
 #pragma unroll 1
   for (int c = it.c0 - 1; c < it.c1; c++) {
     const bool more = c + 1 < it.c1;
     if (more) {                          // asynchronous: these stay in flight across the call (see cp_async8)
       const long o = cell_off(c + HS), om = (long)(c + 1) * sd;
+      if (PAIR) {
+        cp_async8(stg, tq + tb[0] + o);
+        cp_async8(stg + MT, tq + tb[1] + o);
+        cp_async8(stg + 2 * MT, rho + base[0] + o);
+        cp_async8(stg + 3 * MT, a.mflux + base[0] + om);
+      } else {
 #pragma unroll
-      for (int v = 0; v < NL; v++) {
-        cp_async8(stg + (3 * v) * MT, tq + base[v] + o);
-        cp_async8(stg + (3 * v + 1) * MT, rho + base[v] + o);
-        cp_async8(stg + (3 * v + 2) * MT, a.mflux + base[v] + om);
+        for (int v = 0; v < NL; v++) {
+          cp_async8(stg + (3 * v) * MT, tq + tb[v] + o);
+          cp_async8(stg + (3 * v + 1) * MT, rho + base[v] + o);
+          cp_async8(stg + (3 * v + 2) * MT, a.mflux + base[v] + om);
+        }
       }
     }
     const typename MatSel<ORD, VT>::type mat = MatSel<ORD, VT>::get(a.vtab, a.vst, voff, c + 1);
     EOn<NL> eo;
     if constexpr (VT == 0) eo = weno_ring<ORD, NL>(rb, head, mat); else eo = weno_ring_inl<ORD, NL>(rb, head, mat);
     // tracers carry arbitrary units (number concentrations ...): a magnitude that overflows the fast weights gives NaN or
-    // inf -- one test for both lines (a sum that overflows by itself only sends finite values through the slow path too)
+    // inf -- one test for both reconstructions (a sum that overflows by itself only sends finite values through the slow
+    // path too)
     if (!(fabs(eo.E[0]) + fabs(eo.E[1]) <= 1.7976931348623157e308)) {
 #pragma unroll
       for (int v = 0; v < NL; v++) {
@@ -548,23 +573,30 @@ k_march_tracer(const Geom g, const TracerSweepArgs a) {
       if (c >= it.c0) {
         double flux = rn[v] * (rn[v] > 0.0 ? Rp[v] : E - O);
         if (DIR == 2 && c == 0) flux = 0.0;                     // bottom wall: rw = 0 (Dycore.h:477,482)
-        fl[base[v] + (long)c * sd] = flux;
+        fl[fb[v] + (long)c * sd] = flux;
       }
       Rp[v] = E + O;
     }
     if (more) {
       cp_async_wait();
+      if (PAIR) {
+        const double rinv = rcp_pos(stg[2 * MT]);                 // Dycore.h:320
+        rb[head * MT] = stg[0] * rinv;
+        rb[(ORD + head) * MT] = stg[MT] * rinv;
+        rn[0] = rn[1] = stg[3 * MT];                              // mass flux of interface c+1
+      } else {
 #pragma unroll
-      for (int v = 0; v < NL; v++) {
-        rb[(v * ORD + head) * MT] = stg[(3 * v) * MT] * rcp_pos(stg[(3 * v + 1) * MT]);   // Dycore.h:320
-        rn[v] = stg[(3 * v + 2) * MT];                            // mass flux of interface c+1
+        for (int v = 0; v < NL; v++) {
+          rb[(v * ORD + head) * MT] = stg[(3 * v) * MT] * rcp_pos(stg[(3 * v + 1) * MT]);   // Dycore.h:320
+          rn[v] = stg[(3 * v + 2) * MT];                            // mass flux of interface c+1
+        }
       }
       head = head + 1 == ORD ? 0 : head + 1;
     }
   }
   if (DIR == 2 && it.c1 == n) {                                 // top wall: rw = 0 (Dycore.h:496)
 #pragma unroll
-    for (int v = 0; v < NL; v++) fl[base[v] + (long)n * sd] = 0.0;
+    for (int v = 0; v < NL; v++) fl[fb[v] + (long)n * sd] = 0.0;
   }
 }
 

@@ -61,14 +61,21 @@ void OrdLaunch<ORD>::march_state(cudaStream_t s, const Geom &g, const Phys &ph, 
 }
 
 template <int ORD>
-void OrdLaunch<ORD>::march_tracer(cudaStream_t s, const Geom &g, const TracerSweepArgs &a, int dir, int vt) {
-  const dim3 blocks = march_grid(g, dir, a.sbits, a.labits, a.ntr, 2);
+void OrdLaunch<ORD>::march_tracer(cudaStream_t s, const Geom &g, const TracerSweepArgs &a, int dir, int vt, bool pair) {
+  // pair: a.ntr (even) tracers, two per warp on one line; else two adjacent lines of one tracer per warp
+  const dim3 blocks = pair ? march_grid(g, dir, a.sbits, a.labits, a.ntr / 2, 1) : march_grid(g, dir, a.sbits, a.labits, a.ntr, 2);
   constexpr size_t B = MarchCfg<ORD>::SMEM_TRACER;
-  if (dir == 0) AWFL_LAUNCH_MARCH((k_march_tracer<ORD, 0, 0>), B, g, a);
-  else if (dir == 1) AWFL_LAUNCH_MARCH((k_march_tracer<ORD, 1, 0>), B, g, a);
-  else if (vt == 1) AWFL_LAUNCH_MARCH((k_march_tracer<ORD, 2, 1>), B, g, a);
-  else if (vt == 3) AWFL_LAUNCH_MARCH((k_march_tracer<ORD, 2, 3>), B, g, a);
-  else AWFL_LAUNCH_MARCH((k_march_tracer<ORD, 2, 2>), B, g, a);
+#define AWFL_TRACER_CASE(D, V)                                                       \
+  do {                                                                               \
+    if (pair) AWFL_LAUNCH_MARCH((k_march_tracer<ORD, D, V, true>), B, g, a);         \
+    else AWFL_LAUNCH_MARCH((k_march_tracer<ORD, D, V, false>), B, g, a);             \
+  } while (0)
+  if (dir == 0) AWFL_TRACER_CASE(0, 0);
+  else if (dir == 1) AWFL_TRACER_CASE(1, 0);
+  else if (vt == 1) AWFL_TRACER_CASE(2, 1);
+  else if (vt == 3) AWFL_TRACER_CASE(2, 3);
+  else AWFL_TRACER_CASE(2, 2);
+#undef AWFL_TRACER_CASE
 }
 
 template <int ORD>
@@ -86,11 +93,15 @@ void OrdLaunch<ORD>::configure() {
   AWFL_CONFIGURE_2D(2, 2, 1);
   AWFL_CONFIGURE_2D(2, 2, 2);
 #undef AWFL_CONFIGURE_2D
-  configure_march(k_march_tracer<ORD, 0, 0>, BT);
-  configure_march(k_march_tracer<ORD, 1, 0>, BT);
-  configure_march(k_march_tracer<ORD, 2, 1>, BT);
-  configure_march(k_march_tracer<ORD, 2, 2>, BT);
-  configure_march(k_march_tracer<ORD, 2, 3>, BT);
+#define AWFL_CONFIGURE_TR(D, V)                                  \
+  configure_march(k_march_tracer<ORD, D, V, false>, BT);         \
+  configure_march(k_march_tracer<ORD, D, V, true>, BT)
+  AWFL_CONFIGURE_TR(0, 0);
+  AWFL_CONFIGURE_TR(1, 0);
+  AWFL_CONFIGURE_TR(2, 1);
+  AWFL_CONFIGURE_TR(2, 2);
+  AWFL_CONFIGURE_TR(2, 3);
+#undef AWFL_CONFIGURE_TR
 }
 
 template <int ORD>

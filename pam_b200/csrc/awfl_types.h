@@ -68,7 +68,7 @@ struct HydroArgs {
 template <int ORD> struct OrdLaunch {
   // cell-centred marching kernels (awfl_march.cuh); vt: 0 constant horizontal, 1 constant-bank vertical, 2 global vertical
   static void march_state(cudaStream_t s, const Geom &g, const Phys &ph, const SweepArgs &a, int dir, int mode, int vt);
-  static void march_tracer(cudaStream_t s, const Geom &g, const TracerSweepArgs &a, int dir, int vt);
+  static void march_tracer(cudaStream_t s, const Geom &g, const TracerSweepArgs &a, int dir, int vt, bool pair);
   static void configure();   // per-device kernel attributes (shared-memory rings) of every marching kernel of this order
   static int upload_cvtab(const double *host, size_t ndoubles, const int *level_offsets, size_t nlevels);   // synchronous; returns a cudaError_t
   // one PAGE of the table (the levels a segment of the vertical marches needs), asynchronously on the launching stream

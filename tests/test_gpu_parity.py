@@ -388,6 +388,25 @@ def test_first_tracer_in_the_2d_state_march_agrees_with_the_tracer_march(ord, nt
         assert rel_l2(out["1"][k], ref[k], fl[k]) <= 2 * TOL_STEP, (k, rel_l2(out["1"][k], ref[k], fl[k]))
 
 
+@pytest.mark.parametrize("ord,ny,nx,nz,nens", [(5, 1, 18, 14, 40), (5, 5, 6, 8, 33), (9, 1, 12, 40, 33), (3, 1, 18, 14, 40)])
+def test_tracer_pairs_give_the_bits_of_the_two_line_march(ord, ny, nx, nz, nens, monkeypatch):
+    """The tracer march takes two tracers per warp on one line (they share the line's density, its reciprocal and the mass
+    flux) and leaves an odd tracer to the two-lines-of-one-tracer form (AWFL_TRACER_PAIRS=0: every tracer in that form).
+    Each reconstruction sees the same values through the same code: identical bits. 10 tracers: 9 after the first rode in
+    the 2-D state march (4 pairs + 1), 10 in 3-D (5 pairs); member-dependent grid; ord 9 at 40 levels (global table)."""
+    case = _case(nz=nz, ny=ny, nx=nx, nens=nens, nt=10, per_ens=(ord == 5 and ny == 1))
+    out = {}
+    for pairs in ("1", "0"):
+        monkeypatch.setenv("AWFL_TRACER_PAIRS", pairs)
+        c, d = H.make_gpu(case, ord, crm_dt=2.0)
+        d.declare_current_profile_as_hydrostatic(c)
+        for _ in range(2):
+            d.timeStep(c)
+        out[pairs] = H.gpu_fields(c)
+    for k in out["0"]:
+        assert np.array_equal(out["1"][k], out["0"][k]), k
+
+
 def test_errors_are_reported_not_swallowed():
     from pam_b200 import PamCoupler, Dycore
     c = PamCoupler("cuda:0")
